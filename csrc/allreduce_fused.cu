@@ -1,0 +1,331 @@
+// K1 — the data-parallel hot path: cross-GPU gradient allreduce fused with the 1/N average,
+// the L2 weight-decay term, the optimizer update (SGD / momentum / Adam), the staircase LR
+// schedule and the fp32 -> bf16 shadow-weight cast, in ONE kernel that reads and writes peer
+// GPUs' buffers directly over NVLink (CUDA-IPC mapped pointers).  No NCCL call and no separate
+// elementwise kernel runs on this path.
+//
+// What it replaces in the reference: Gather to rank 0 over host MPI (mpipy.py:121-127), the
+// NumPy mean on one CPU thread (mpipy.py:130-136), the H2D tf.assign on root only
+// (mpipy.py:138-152), the L2 gradient (mpipy.py:57-58), exponential_decay (mpipy.py:60-64) and
+// ApplyMomentum (mpipy.py:65-66).
+//
+// Algorithms (chosen per bucket size by the caller):
+//   one-shot  every rank loads the bucket from all N peers, reduces in rank order in fp32
+//             registers and updates its own replica.  (N-1)*S bytes inbound, one signal round
+//             before and one after.  Optimizer slots replicated.
+//   two-shot  rank r owns slice r: reduce-scatter by peer loads, update the slice, all-gather
+//             by peer stores of the new fp32 master + bf16 shadow into every replica.
+//             2*(N-1)/N*S bytes per GPU.  Optimizer slots sharded (ZeRO-1 style).
+//   nvls      as two-shot, but multimem.ld_reduce pulls the switch-reduced slice in one load
+//             and multimem.st broadcasts the result (needs a multicast mapping).
+// Every rank sums in the same order, so replicas stay bit-identical.
+//
+// Flag protocol: one 32-bit slot per (block, peer) in each rank's signal pad, written with
+// st.release.sys after a system fence and polled with ld.acquire.sys.  Values are a per-block
+// sequence number that only grows (2 per launch), so nothing is ever reset and CUDA-graph
+// replays are safe.  Every spin is bounded; on expiry the status word is set and the kernel
+// finishes instead of hanging the GPU (SURVEY section 5 "failure detection").
+#include "common.cuh"
+
+namespace {
+
+using namespace mtb;
+
+constexpr int kMaxRanks = 16;
+constexpr int kMaxBlocks = 256;
+constexpr int kMaxRanges = 8;
+constexpr long long kSpinLimit = 6000000000ll;      // ~3 s
+
+struct FusedParams {
+  int world, rank, algo, optimizer;                 // optimizer: -1 none (plain allreduce), 0 sgd, 1 momentum, 2 adam
+  const float* grads[kMaxRanks];                    // per-rank flat fp32 gradient buffers (peer mapped)
+  float* params[kMaxRanks];                         // per-rank flat fp32 master parameters / allreduce output
+  __nv_bfloat16* shadow[kMaxRanks];                 // per-rank bf16 shadow weights (may be null)
+  const float* mc_grads;                            // multicast views (nvls only)
+  float* mc_params;
+  __nv_bfloat16* mc_shadow;
+  float* slot_m;
+  float* slot_v;
+  uint32_t* flags[kMaxRanks];                       // signal pads [kMaxBlocks][kMaxRanks]
+  uint32_t* seq;                                    // local per-block sequence numbers [kMaxBlocks]
+  int* status;
+  long long offset, count;                          // bucket range in elements, multiples of 4
+  float scale;                                      // 1/N (or 1 for a plain sum)
+  float lr0, lr_decay, lr_override;
+  int batch;
+  long long decay_rows;
+  const long long* step_ptr;
+  float momentum, beta1, beta2, eps, wd;
+  int n_ranges;
+  long long range_begin[kMaxRanges], range_end[kMaxRanges];   // where the L2 term applies
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* p, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+// All ranks' block `b` meet here.  Every thread fences its own prior stores first.
+__device__ void cross_gpu_barrier(const FusedParams& p, int b, uint32_t val) {
+  __threadfence_system();
+  __syncthreads();
+  if ((int)threadIdx.x < p.world) {
+    const int peer = threadIdx.x;
+    st_release_sys(p.flags[peer] + b * kMaxRanks + p.rank, val);
+    const uint32_t* mine = p.flags[p.rank] + b * kMaxRanks + peer;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(mine) - val) < 0) {
+      if (clock64() - t0 > kSpinLimit) {
+        atomicExch(p.status, MTB_E_TIMEOUT);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+struct Hyper {
+  float lr, bc_lr;      // bc_lr: Adam's bias-corrected step size
+};
+
+__device__ __forceinline__ Hyper make_hyper(const FusedParams& p) {
+  Hyper h;
+  const long long step = p.step_ptr ? *p.step_ptr : 0;
+  float lr = p.lr0;
+  if (p.lr_override >= 0.f) {
+    lr = p.lr_override;
+  } else if (p.decay_rows > 0 && p.lr_decay != 1.0f) {
+    // tf.train.exponential_decay(lr0, step*batch, decay_rows, decay, staircase=True), fp32 like TF
+    const float e = floorf((float)step * (float)p.batch / (float)p.decay_rows);
+    lr = p.lr0 * powf(p.lr_decay, e);
+  }
+  h.lr = lr;
+  const float t = (float)(step + 1);
+  h.bc_lr = lr * sqrtf(1.0f - powf(p.beta2, t)) / (1.0f - powf(p.beta1, t));
+  return h;
+}
+
+__device__ __forceinline__ bool decays(const FusedParams& p, long long i) {
+  bool d = false;
+#pragma unroll
+  for (int r = 0; r < kMaxRanges; ++r)
+    if (r < p.n_ranges && i >= p.range_begin[r] && i < p.range_end[r]) d = true;
+  return d;
+}
+
+// One float4 of the optimizer.  g is the already averaged gradient.
+__device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g) {
+  float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
+  if (p.optimizer < 0) return g;
+  if (p.wd != 0.f && decays(p, i)) {            // L2 term: grad += wd * w (mpipy.py:57-58)
+    g.x = fmaf(p.wd, w.x, g.x); g.y = fmaf(p.wd, w.y, g.y); g.z = fmaf(p.wd, w.z, g.z); g.w = fmaf(p.wd, w.w, g.w);
+  }
+  if (p.optimizer == 0) {
+    w.x -= h.lr * g.x; w.y -= h.lr * g.y; w.z -= h.lr * g.z; w.w -= h.lr * g.w;
+  } else if (p.optimizer == 1) {                // accum = m*accum + g; w -= lr*accum (mpipy.py:65)
+    float4 m = *reinterpret_cast<float4*>(p.slot_m + i);
+    m.x = fmaf(p.momentum, m.x, g.x); m.y = fmaf(p.momentum, m.y, g.y);
+    m.z = fmaf(p.momentum, m.z, g.z); m.w = fmaf(p.momentum, m.w, g.w);
+    *reinterpret_cast<float4*>(p.slot_m + i) = m;
+    w.x -= h.lr * m.x; w.y -= h.lr * m.y; w.z -= h.lr * m.z; w.w -= h.lr * m.w;
+  } else {
+    float4 m = *reinterpret_cast<float4*>(p.slot_m + i);
+    float4 v = *reinterpret_cast<float4*>(p.slot_v + i);
+    const float b1 = p.beta1, b2 = p.beta2, c1 = 1.f - b1, c2 = 1.f - b2;
+    m.x = b1 * m.x + c1 * g.x; m.y = b1 * m.y + c1 * g.y; m.z = b1 * m.z + c1 * g.z; m.w = b1 * m.w + c1 * g.w;
+    v.x = b2 * v.x + c2 * g.x * g.x; v.y = b2 * v.y + c2 * g.y * g.y;
+    v.z = b2 * v.z + c2 * g.z * g.z; v.w = b2 * v.w + c2 * g.w * g.w;
+    *reinterpret_cast<float4*>(p.slot_m + i) = m;
+    *reinterpret_cast<float4*>(p.slot_v + i) = v;
+    w.x -= h.bc_lr * m.x / (sqrtf(v.x) + p.eps); w.y -= h.bc_lr * m.y / (sqrtf(v.y) + p.eps);
+    w.z -= h.bc_lr * m.z / (sqrtf(v.z) + p.eps); w.w -= h.bc_lr * m.w / (sqrtf(v.w) + p.eps);
+  }
+  return w;
+}
+
+__device__ __forceinline__ uint2 to_bf16x4(float4 w) {
+  return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+}
+
+__global__ void __launch_bounds__(512)
+fused_allreduce_update_kernel(const FusedParams p) {
+  const int b = blockIdx.x;
+  __shared__ uint32_t s_seq;
+  if (threadIdx.x == 0) s_seq = p.seq[b];
+  __syncthreads();
+  const uint32_t seq = s_seq;
+  const Hyper h = make_hyper(p);
+  const bool multi = p.world > 1;
+  if (multi) cross_gpu_barrier(p, b, seq + 1);       // every peer's gradients are complete
+
+  const long long vec_total = p.count >> 2;
+  if (!multi || p.algo == 0) {
+    // ---- one-shot (and the single-GPU fused optimizer) ----
+    for (long long v = (long long)b * blockDim.x + threadIdx.x; v < vec_total; v += (long long)gridDim.x * blockDim.x) {
+      const long long i = p.offset + (v << 2);
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!multi) {
+        g = *reinterpret_cast<const float4*>(p.grads[0] + i);
+      } else {
+#pragma unroll 4
+        for (int r = 0; r < p.world; ++r) {
+          const float4 t = ld_peer_f4(p.grads[r] + i);
+          g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        }
+      }
+      g.x *= p.scale; g.y *= p.scale; g.z *= p.scale; g.w *= p.scale;
+      const float4 w = apply_update(p, h, i, g);
+      *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
+      if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = to_bf16x4(w);
+    }
+  } else {
+    // ---- two-shot / nvls: this rank owns one contiguous slice ----
+    const long long per = (vec_total + p.world - 1) / p.world;
+    const long long lo = per * p.rank < vec_total ? per * p.rank : vec_total;
+    const long long hi = lo + per < vec_total ? lo + per : vec_total;
+    for (long long v = lo + (long long)b * blockDim.x + threadIdx.x; v < hi; v += (long long)gridDim.x * blockDim.x) {
+      const long long i = p.offset + (v << 2);
+      float4 g;
+      if (p.algo == 2) {
+        g = multimem_ld_reduce_f4(p.mc_grads + i);
+      } else {
+        g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+        for (int r = 0; r < p.world; ++r) {
+          const float4 t = ld_peer_f4(p.grads[r] + i);
+          g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        }
+      }
+      g.x *= p.scale; g.y *= p.scale; g.z *= p.scale; g.w *= p.scale;
+      const float4 w = apply_update(p, h, i, g);
+      const uint2 wb = to_bf16x4(w);
+      if (p.algo == 2) {
+        multimem_st_f4(p.mc_params + i, w);
+        if (p.mc_shadow) multimem_st_bf16x4(p.mc_shadow + i, wb);
+      } else {
+#pragma unroll 4
+        for (int r = 0; r < p.world; ++r) {
+          *reinterpret_cast<float4*>(p.params[r] + i) = w;
+          if (p.shadow[r]) *reinterpret_cast<uint2*>(p.shadow[r] + i) = wb;
+        }
+      }
+    }
+  }
+  if (multi) cross_gpu_barrier(p, b, seq + 2);       // peers are done reading my grads / writing my params
+  if (threadIdx.x == 0) p.seq[b] = seq + 2;
+}
+
+__global__ void barrier_kernel(const FusedParams p) {
+  __shared__ uint32_t s_seq;
+  if (threadIdx.x == 0) s_seq = p.seq[0];
+  __syncthreads();
+  const uint32_t seq = s_seq;
+  cross_gpu_barrier(p, 0, seq + 2);
+  if (threadIdx.x == 0) p.seq[0] = seq + 2;
+}
+
+__global__ void advance_step_kernel(long long* step) { *step += 1; }
+
+}  // namespace
+
+extern "C" {
+
+static int fill(const mtb_fused_args* a, FusedParams* p) {
+  MTB_REQUIRE(a->world >= 1 && a->world <= kMaxRanks && a->rank >= 0 && a->rank < a->world, "fused: bad world/rank");
+  MTB_REQUIRE(a->offset % 4 == 0 && a->count % 4 == 0 && a->count >= 0, "fused: offset/count must be multiples of 4");
+  MTB_REQUIRE(a->n_ranges >= 0 && a->n_ranges <= kMaxRanges, "fused: too many decay ranges");
+  MTB_REQUIRE(a->algo != 2 || (a->mc_grads && a->mc_params), "fused: nvls needs multicast pointers");
+  p->world = a->world; p->rank = a->rank; p->algo = a->algo; p->optimizer = a->optimizer;
+  for (int r = 0; r < kMaxRanks; ++r) {
+    p->grads[r] = reinterpret_cast<const float*>(a->grads[r]);
+    p->params[r] = reinterpret_cast<float*>(a->params[r]);
+    p->shadow[r] = reinterpret_cast<__nv_bfloat16*>(a->shadow[r]);
+    p->flags[r] = reinterpret_cast<uint32_t*>(a->flags[r]);
+  }
+  p->mc_grads = reinterpret_cast<const float*>(a->mc_grads);
+  p->mc_params = reinterpret_cast<float*>(a->mc_params);
+  p->mc_shadow = reinterpret_cast<__nv_bfloat16*>(a->mc_shadow);
+  p->slot_m = reinterpret_cast<float*>(a->slot_m);
+  p->slot_v = reinterpret_cast<float*>(a->slot_v);
+  p->seq = reinterpret_cast<uint32_t*>(a->seq);
+  p->status = reinterpret_cast<int*>(a->status);
+  p->offset = a->offset; p->count = a->count; p->scale = a->scale;
+  p->lr0 = a->lr0; p->lr_decay = a->lr_decay; p->lr_override = a->lr_override;
+  p->batch = a->batch; p->decay_rows = a->decay_rows;
+  p->step_ptr = reinterpret_cast<const long long*>(a->step_ptr);
+  p->momentum = a->momentum; p->beta1 = a->beta1; p->beta2 = a->beta2; p->eps = a->eps; p->wd = a->wd;
+  p->n_ranges = a->n_ranges;
+  for (int r = 0; r < kMaxRanges; ++r) { p->range_begin[r] = a->range_begin[r]; p->range_end[r] = a->range_end[r]; }
+  return 0;
+}
+
+int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
+  FusedParams p;
+  int e = fill(a, &p);
+  if (e) return e;
+  MTB_REQUIRE(p.optimizer < 1 || p.slot_m, "fused: momentum/adam need slot_m");
+  MTB_REQUIRE(p.optimizer < 2 || p.slot_v, "fused: adam needs slot_v");
+  MTB_REQUIRE(p.world == 1 || (p.seq && p.status && p.flags[p.rank]), "fused: multi-GPU needs flags/seq/status");
+  MTB_REQUIRE(p.seq, "fused: seq buffer required");
+  if (p.count == 0) return 0;
+  int block = a->block > 0 ? a->block : 512;
+  long long vecs = p.count >> 2;
+  if (p.world > 1 && p.algo != 0) vecs = (vecs + p.world - 1) / p.world;
+  int grid = a->grid > 0 ? a->grid : 148;
+  long long need = (vecs + block - 1) / block;
+  if (need < 1) need = 1;
+  if (grid > need) grid = (int)need;
+  if (grid > kMaxBlocks) grid = kMaxBlocks;
+  fused_allreduce_update_kernel<<<grid, block, 0, stream>>>(p);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream) {
+  FusedParams p;
+  int e = fill(a, &p);
+  if (e) return e;
+  if (p.world == 1) return 0;
+  barrier_kernel<<<1, 32, 0, stream>>>(p);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_advance_step(long long* step_ptr, cudaStream_t stream) {
+  advance_step_kernel<<<1, 1, 0, stream>>>(step_ptr);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_fused_max_blocks(void) { return kMaxBlocks; }
+int mtb_fused_flag_bytes(void) { return kMaxBlocks * kMaxRanks * (int)sizeof(uint32_t); }
+
+}  // extern "C"

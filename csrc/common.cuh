@@ -1,0 +1,82 @@
+// Shared device/host helpers for libmtb200.so (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../include/mtb200.h"
+
+#define MTB_CUDA_CHECK(expr)                                  \
+  do {                                                        \
+    cudaError_t _e = (expr);                                  \
+    if (_e != cudaSuccess) return mtb_set_error(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define MTB_LAUNCH_CHECK() MTB_CUDA_CHECK(cudaGetLastError())
+
+#define MTB_REQUIRE(cond, msg)                                \
+  do {                                                        \
+    if (!(cond)) return mtb_set_error_msg(MTB_E_ARG, msg, __FILE__, __LINE__); \
+  } while (0)
+
+int mtb_set_error(cudaError_t e, const char* expr, const char* file, int line);
+int mtb_set_error_msg(int code, const char* msg, const char* file, int line);
+
+namespace mtb {
+
+constexpr int kNumSMs = 148;
+
+__host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// ---- Philox4x32-10: identical to utils/philox.py ------------------------------
+struct Philox {
+  static constexpr uint32_t kM0 = 0xD2511F53u, kM1 = 0xCD9E8D57u;
+  static constexpr uint32_t kW0 = 0x9E3779B9u, kW1 = 0xBB67AE85u;
+  __device__ static inline uint4 gen(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                     uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      uint32_t hi0 = __umulhi(kM0, c0), lo0 = kM0 * c0;
+      uint32_t hi1 = __umulhi(kM1, c2), lo1 = kM1 * c2;
+      uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+      c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+      k0 += kW0; k1 += kW1;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+};
+
+enum : uint32_t { kPurposeDropout = 1, kPurposeInit = 2, kPurposeData = 3 };
+
+__device__ inline float u32_to_unit(uint32_t w) { return (float)(w >> 8) * (1.0f / 16777216.0f); }
+
+// Four consecutive keep decisions for elements 4*blk .. 4*blk+3 of dropout stream `step`.
+__device__ inline uint4 dropout_words(uint32_t blk, uint64_t seed, uint64_t step) {
+  return Philox::gen(blk, (uint32_t)step, (uint32_t)(step >> 32), kPurposeDropout, (uint32_t)seed,
+                     (uint32_t)(seed >> 32));
+}
+
+__device__ inline float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ inline float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ inline uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__device__ inline float2 unpack_bf16x2(uint32_t w) {
+  __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&w);
+  return __bfloat1622float2(v);
+}
+
+}  // namespace mtb

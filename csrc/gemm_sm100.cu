@@ -1,0 +1,352 @@
+// tcgen05 GEMM engine: D[M,N] = op(A) * op(B) with bf16 operands and fp32 accumulation in
+// tensor memory.  One kernel, warp-specialised:
+//   warp 0     TMA producer   global -> 128B-swizzled shared tiles, multi-stage mbarrier ring
+//   warp 1     MMA issuer     one elected thread issues tcgen05.mma (M=128, N=BN, K=16) x4 per stage
+//   warps 2-5  epilogue       tcgen05.ld TMEM -> registers -> bias / ReLU / dropout / cast -> global
+// Either operand may be K-major ("row = M/N index, K contiguous") or MN-major ("row = K index,
+// M/N contiguous"); TMA lands both in the canonical SWIZZLE_128B layouts so no transposes are
+// ever materialised.  That covers every FC product of the network with ONE bf16 weight copy:
+//   fprop  Y = X * W          A K-major [B,in],  B MN-major W[in,out]      (mpipy.py:165,167)
+//   dgrad  dX = dY * W^T      A K-major [B,out], B K-major  W[in,out]      (TF MatMul grad)
+//   wgrad  dW = X^T * dY      A MN-major X[B,in], B MN-major dY[B,out]
+// and, through im2col, the generic convolution path (mpipy.py:156,159).
+// Split-K: each split writes its fp32 partial tile to a workspace; the last CTA to arrive at a
+// per-tile counter sums the partials in split order (deterministic) and runs the epilogue.
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+#include "sm100.cuh"
+#include "tma_host.cuh"
+
+namespace {
+
+using namespace sm100;
+
+constexpr int BM = 128;
+constexpr int BK = 64;                 // bf16 elements per stage along K = one 128-byte swizzle row
+constexpr int kThreads = 192;
+
+struct GemmParams {
+  int M, N, K;
+  int kb_total, kb_per_split, splits;
+  void* out;
+  long long ldc;
+  int out_bf16;
+  const float* bias;
+  int relu;
+  float keep_prob;
+  unsigned long long seed;
+  const long long* step_ptr;
+  float* workspace;
+  unsigned int* counters;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = BN == 128 ? 4 : 6;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 256;
+};
+
+__device__ __forceinline__ void epilogue_store(const GemmParams& p, const float (&v)[32], int grow, int gcol0,
+                                               unsigned long long step) {
+  if (grow >= p.M) return;
+  float o[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    float x = v[j];
+    int c = gcol0 + j;
+    if (p.bias != nullptr && c < p.N) x += __ldg(p.bias + c);
+    if (p.relu) x = fmaxf(x, 0.f);
+    o[j] = x;
+  }
+  if (p.keep_prob < 1.0f) {
+    const float inv = 1.0f / p.keep_prob;
+#pragma unroll
+    for (int j4 = 0; j4 < 8; ++j4) {
+      unsigned long long e = (unsigned long long)grow * (unsigned long long)p.N + (unsigned)(gcol0 + 4 * j4);
+      uint4 w = mtb::dropout_words((uint32_t)(e >> 2), p.seed, step);
+      o[4 * j4 + 0] = mtb::u32_to_unit(w.x) < p.keep_prob ? o[4 * j4 + 0] * inv : 0.f;
+      o[4 * j4 + 1] = mtb::u32_to_unit(w.y) < p.keep_prob ? o[4 * j4 + 1] * inv : 0.f;
+      o[4 * j4 + 2] = mtb::u32_to_unit(w.z) < p.keep_prob ? o[4 * j4 + 2] * inv : 0.f;
+      o[4 * j4 + 3] = mtb::u32_to_unit(w.w) < p.keep_prob ? o[4 * j4 + 3] * inv : 0.f;
+    }
+  }
+  const bool full = (gcol0 + 32 <= p.N);
+  if (p.out_bf16) {
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)grow * p.ldc + gcol0;
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint4 q;
+        q.x = mtb::pack_bf16x2(o[8 * j + 0], o[8 * j + 1]);
+        q.y = mtb::pack_bf16x2(o[8 * j + 2], o[8 * j + 3]);
+        q.z = mtb::pack_bf16x2(o[8 * j + 4], o[8 * j + 5]);
+        q.w = mtb::pack_bf16x2(o[8 * j + 6], o[8 * j + 7]);
+        reinterpret_cast<uint4*>(dst)[j] = q;
+      }
+    } else {
+      for (int j = 0; j < 32 && gcol0 + j < p.N; ++j) dst[j] = __float2bfloat16(o[j]);
+    }
+  } else {
+    float* dst = reinterpret_cast<float*>(p.out) + (long long)grow * p.ldc + gcol0;
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        reinterpret_cast<float4*>(dst)[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+    } else {
+      for (int j = 0; j < 32 && gcol0 + j < p.N; ++j) dst[j] = o[j];
+    }
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 const GemmParams p) {
+  using C = Cfg<BN>;
+  constexpr int S = C::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + S * C::kABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + S * C::kBBytes);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* tmem_full = empty_bar + S;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  volatile int* last_flag = reinterpret_cast<volatile int*>(tmem_holder + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile_m = blockIdx.x, tile_n = blockIdx.y, split = blockIdx.z;
+  const int kb0 = split * p.kb_per_split;
+  const int nkb = min(p.kb_per_split, p.kb_total - kb0);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<BN>(tmem_holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % S, ph = (i / S) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full_bar[s], C::kABytes + C::kBBytes);
+        const int kc = (kb0 + i) * BK;
+        uint8_t* a = sA + s * C::kABytes;
+        uint8_t* b = sB + s * C::kBBytes;
+        if (!A_MN) {
+          tma_load_2d(a, &tma_a, &full_bar[s], kc, tile_m * BM);
+        } else {
+          tma_load_2d(a, &tma_a, &full_bar[s], tile_m * BM, kc);
+          tma_load_2d(a + 8192, &tma_a, &full_bar[s], tile_m * BM + 64, kc);
+        }
+        if (!B_MN) {
+          tma_load_2d(b, &tma_b, &full_bar[s], kc, tile_n * BN);
+        } else {
+#pragma unroll
+          for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tma_b, &full_bar[s], tile_n * BN + h * 64, kc);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, BM, BN, A_MN, B_MN);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % S, ph = (i / S) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA + s * C::kABytes);
+        const uint32_t b_base = smem_u32(sB + s * C::kBBytes);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          const uint64_t da = A_MN ? make_smem_desc(a_base + k * 2048, 8192, 1024, kSwizzle128B)
+                                   : make_smem_desc(a_base + k * 32, 16, 1024, kSwizzle128B);
+          const uint64_t db = B_MN ? make_smem_desc(b_base + k * 2048, 8192, 1024, kSwizzle128B)
+                                   : make_smem_desc(b_base + k * 32, 16, 1024, kSwizzle128B);
+          mma_f16(tmem_base, da, db, idesc, (i | k) != 0);
+        }
+        mma_commit(&empty_bar[s]);       // smem slot reusable once these MMAs retire
+      }
+      mma_commit(tmem_full);             // accumulator complete
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;              // TMEM lane quadrant this warp may read
+    const int row = q * 32 + lane;
+    const int grow = tile_m * BM + row;
+    const unsigned long long step = p.step_ptr ? (unsigned long long)*p.step_ptr : 0ull;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    if (p.splits == 1) {
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        epilogue_store(p, v, grow, tile_n * BN + c * 32, step);
+      }
+    } else {
+      const int tile_id = tile_m * gridDim.y + tile_n;
+      float* ws = p.workspace + ((size_t)(tile_id * p.splits + split) * BM + row) * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          __stcg(reinterpret_cast<float4*>(ws + c * 32) + j,
+                 make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                             __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3])));
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) {
+        unsigned old = atomicAdd(&p.counters[tile_id], 1u);
+        *last_flag = (old == (unsigned)(p.splits - 1)) ? 1 : 0;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*last_flag) {
+        __threadfence();
+        const float* base = p.workspace + ((size_t)tile_id * p.splits * BM + row) * BN;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+          for (int s = 0; s < p.splits; ++s) {
+            const float4* src = reinterpret_cast<const float4*>(base + (size_t)s * BM * BN + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 t = __ldcg(src + j);
+              v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+            }
+          }
+          epilogue_store(p, v, grow, tile_n * BN + c * 32, step);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) p.counters[tile_id] = 0u;     // self-cleaning for the next launch
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<BN>(tmem_base);
+  }
+}
+
+// ---- tensor-map cache ------------------------------------------------------------------------
+struct MapKey {
+  const void* base; uint64_t rows, cols, pitch; uint32_t box_rows, box_cols;
+  bool operator<(const MapKey& o) const {
+    return std::tie(base, rows, cols, pitch, box_rows, box_cols) <
+           std::tie(o.base, o.rows, o.cols, o.pitch, o.box_rows, o.box_cols);
+  }
+};
+std::map<MapKey, CUtensorMap> g_maps;
+std::mutex g_maps_mu;
+
+bool get_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
+             uint32_t box_rows, uint32_t box_cols) {
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  MapKey k{base, rows, cols, pitch_bytes, box_rows, box_cols};
+  auto it = g_maps.find(k);
+  if (it != g_maps.end()) { *out = it->second; return true; }
+  CUtensorMap m;
+  if (!tma::make_2d_sw128(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, rows, cols, pitch_bytes, box_rows, box_cols))
+    return false;
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[k] = m;
+  *out = m;
+  return true;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)mtb::ceil_div(p.M, BM), (unsigned)mtb::ceil_div(p.N, BN), (unsigned)p.splits);
+  kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, st>>>(ma, mb, p);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t mtb_gemm_workspace_bytes(int M, int N, int bn, int splits) {
+  if (splits <= 1) return 0;
+  if (bn != 64 && bn != 128) bn = 128;
+  size_t tiles = (size_t)mtb::ceil_div(M, BM) * (size_t)mtb::ceil_div(N, bn);
+  return tiles * (size_t)splits * BM * bn * sizeof(float);
+}
+
+size_t mtb_gemm_counter_bytes(int M, int N, int bn) {
+  if (bn != 64 && bn != 128) bn = 128;
+  return (size_t)mtb::ceil_div(M, BM) * (size_t)mtb::ceil_div(N, bn) * sizeof(unsigned int);
+}
+
+int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major, int b_mn_major,
+                  long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
+                  float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
+                  void* workspace, void* counters, cudaStream_t stream) {
+  MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm: null pointer or empty shape");
+  MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm: operand row pitch must be a multiple of 16 bytes");
+  MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: operands must be 16-byte aligned");
+  if (bn != 64 && bn != 128) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
+  if (splits < 1) splits = 1;
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_total = (int)mtb::ceil_div(K, BK);
+  if (splits > p.kb_total) splits = p.kb_total;
+  p.kb_per_split = (int)mtb::ceil_div(p.kb_total, splits);
+  splits = (int)mtb::ceil_div(p.kb_total, p.kb_per_split);     // no empty split
+  p.splits = splits;
+  MTB_REQUIRE(splits == 1 || (workspace && counters), "gemm: split-K needs workspace and counters");
+  p.out = out; p.ldc = ldc; p.out_bf16 = out_bf16; p.bias = bias; p.relu = relu;
+  p.keep_prob = keep_prob; p.seed = seed; p.step_ptr = step_ptr;
+  p.workspace = reinterpret_cast<float*>(workspace);
+  p.counters = reinterpret_cast<unsigned int*>(counters);
+  CUtensorMap ma, mb;
+  bool ok;
+  // K-major operand stored [MN rows, K cols]; MN-major operand stored [K rows, MN cols]
+  ok = a_mn_major ? get_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, 64, 64)
+                  : get_map(&ma, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, BM, 64);
+  MTB_REQUIRE(ok, "gemm: cuTensorMapEncodeTiled failed for A");
+  ok = b_mn_major ? get_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64, 64)
+                  : get_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, (uint32_t)bn, 64);
+  MTB_REQUIRE(ok, "gemm: cuTensorMapEncodeTiled failed for B");
+#define MTB_GEMM_CASE(BN_, AM_, BM_)                                            \
+  if (bn == BN_ && (a_mn_major != 0) == AM_ && (b_mn_major != 0) == BM_) return launch<BN_, AM_, BM_>(ma, mb, p, stream);
+  MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)
+  MTB_GEMM_CASE(128, true, true) MTB_GEMM_CASE(64, false, false) MTB_GEMM_CASE(64, false, true)
+  MTB_GEMM_CASE(64, true, false) MTB_GEMM_CASE(64, true, true)
+#undef MTB_GEMM_CASE
+  return mtb_set_error_msg(MTB_E_ARG, "gemm: no kernel variant", __FILE__, __LINE__);
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+/* mtb200.h — C ABI of libmtb200.so: the sm_100a kernels and the device runtime.
+ *
+ * Every function returns 0 on success or a non-zero code; mtb_last_error() gives the text.
+ * All pointers are device pointers unless the name says host.  `stream` is a cudaStream_t.
+ * The reference ships no native code; each entry point cites the line
+ * of mpipy.py whose TensorFlow / MPI library call it replaces.
+ */
+#ifndef MTB200_H_
+#define MTB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __DRIVER_TYPES_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+enum {
+  MTB_E_OK = 0,
+  MTB_E_CUDA = 1,     /* a CUDA runtime call failed */
+  MTB_E_ARG = 2,      /* bad argument / unsupported shape */
+  MTB_E_TIMEOUT = 3,  /* a device-side wait on a peer ran out of time */
+  MTB_E_LIMIT = 4     /* request exceeds a fixed capacity */
+};
+
+/* ---- runtime ------------------------------------------------------------------------ */
+const char* mtb_last_error(void);
+int mtb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* total_mem);
+/* static arena (replaces TF's BFC allocator with growth, mpipy.py:69-71): one cudaMalloc,
+ * shapes are static so nothing is ever freed mid-run */
+int mtb_arena_alloc(size_t bytes, void** out_ptr);
+int mtb_arena_free(void* ptr);
+/* CUDA IPC: export / import an arena so peers can map it (replaces host-staged MPI buffers) */
+int mtb_ipc_export(void* ptr, void* out_handle64);
+int mtb_ipc_import(const void* handle64, void** out_ptr);
+int mtb_ipc_close(void* ptr);
+int mtb_enable_peer_access(int peer_device);
+
+/* ---- tcgen05 GEMM engine (cuBLAS matmul behind tf.matmul, mpipy.py:165,167, and its grads) */
+size_t mtb_gemm_workspace_bytes(int M, int N, int bn, int splits);
+size_t mtb_gemm_counter_bytes(int M, int N, int bn);
+int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major, int b_mn_major,
+                  long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
+                  float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
+                  void* workspace, void* counters, cudaStream_t stream);
+
+/* ---- init / data / casts (tf.truncated_normal mpipy.py:38-52; extract_data mpipy.py:215) ---- */
+int mtb_init_trunc_normal(float* dst, long long n, float stddev, unsigned long long seed, unsigned stream_id,
+                          cudaStream_t stream);
+int mtb_fill_f32(float* dst, long long n, float value, cudaStream_t stream);
+int mtb_normalize_u8_dev(const uint8_t* src, float* dst, long long n, cudaStream_t stream);
+int mtb_synthetic_batch(float* images, int* labels, long long n_img, long long row_offset,
+                        unsigned long long seed, int learnable, cudaStream_t stream);
+int mtb_batch_window(const float* data, const int* labels, const long long* step_ptr, long long rows, int B,
+                     float* x_out, int* y_out, cudaStream_t stream);                       /* mpipy.py:80-82 */
+int mtb_cast_f32_to_bf16(const float* src, void* dst, long long n, cudaStream_t stream);
+int mtb_cast_bf16_to_f32(const void* src, float* dst, long long n, cudaStream_t stream);
+int mtb_l2_half_sumsq(const float* x, long long n, float* out_accum, cudaStream_t stream);   /* mpipy.py:57-58 */
+
+/* ---- conv1 fused: conv5x5 + bias + ReLU + 2x2 max-pool, and its wgrad (mpipy.py:156-158) ---- */
+int mtb_conv1_fwd(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B, int C1,
+                  cudaStream_t stream);
+int mtb_conv1_wgrad(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
+                    int B, int C1, cudaStream_t stream);
+
+/* ---- pooling + generic-conv helpers (mpipy.py:158,161; tf.nn.conv2d mpipy.py:159 via im2col) ---- */
+int mtb_maxpool2x2_fwd(const void* in, void* out, uint8_t* idx, int B, int H, int W, int C, cudaStream_t stream);
+int mtb_unpool_relu_bwd(const void* dP, const void* P, const uint8_t* idx, void* dA, int B, int H, int W, int C,
+                        cudaStream_t stream);
+int mtb_im2col_5x5(const void* x, void* col, int B, int H, int W, int C, cudaStream_t stream);
+int mtb_col2im_5x5(const void* dcol, void* dx, int B, int H, int W, int C, cudaStream_t stream);
+
+/* ---- FC2 + softmax + cross-entropy, forward and backward (mpipy.py:167, :55-56, :67-68) ---- */
+int mtb_fc2_softmax_ce(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
+                       float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
+                       cudaStream_t stream);
+int mtb_fc2_dgrad(const float* dlogits, const float* W, const void* h_bf16, void* dh_bf16, int B, int F, int NC,
+                  float scale, cudaStream_t stream);
+int mtb_fc2_wgrad(const void* h_bf16, const float* dlogits, float* dW, float* db, int B, int F, int NC,
+                  cudaStream_t stream);
+int mtb_colsum_bf16(const void* x_bf16, float* out, long long R, int C, cudaStream_t stream);
+
+/* ---- K1: fused cross-GPU allreduce + average + L2 + optimizer + LR schedule + bf16 cast
+ *      (Gather/mean/assign mpipy.py:121-152; l2 mpipy.py:57-58; lr mpipy.py:60-64; momentum mpipy.py:65) */
+typedef struct mtb_fused_args {
+  int world, rank, algo /*0 one-shot, 1 two-shot, 2 nvls*/, optimizer /*-1 none, 0 sgd, 1 momentum, 2 adam*/;
+  const void* grads[16];
+  void* params[16];
+  void* shadow[16];
+  const void* mc_grads;
+  void* mc_params;
+  void* mc_shadow;
+  void* slot_m;
+  void* slot_v;
+  void* flags[16];
+  void* seq;
+  void* status;
+  long long offset, count;
+  float scale, lr0, lr_decay, lr_override;
+  int batch;
+  long long decay_rows;
+  const void* step_ptr;
+  float momentum, beta1, beta2, eps, wd;
+  int n_ranges;
+  long long range_begin[8], range_end[8];
+  int grid, block;
+} mtb_fused_args;
+int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
+int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */
+int mtb_advance_step(long long* step_ptr, cudaStream_t stream);             /* global_step=iter_, mpipy.py:66 */
+int mtb_fused_max_blocks(void);
+int mtb_fused_flag_bytes(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MTB200_H_ */

@@ -1,0 +1,404 @@
+"""GPU engine: the whole train step on hand-written sm_100a kernels.
+
+Replaces the TensorFlow session (``tf.Session`` + ``sess.run``, ``mpipy.py:72-73,85``),
+its autodiff (``minimize``, ``mpipy.py:65``) and its allocator (``mpipy.py:69-71``):
+
+* a static set of buffers sized once from the config (all shapes are static,
+  ``mpipy.py:33-37``) — parameters / gradients / bf16 shadow weights live in
+  symmetric, peer-mapped memory when the world has more than one rank;
+* forward and backward wired kernel by kernel (no autograd on the hot path);
+* the fused allreduce + optimizer kernel K1 as the only synchronisation;
+* the step captured in a CUDA graph: one launch per step, no per-step H2D, the
+  step counter / LR schedule / dropout stream all live on the device.
+
+Precision: bf16 activations and bf16 tensor-core operands, fp32 accumulation,
+fp32 master weights, optimizer state and gradients.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from .config import TrainConfig
+from .models.spec import ModelSpec, flat_size
+from .ops import native as N
+from .parallel.comm import Communicator
+
+_OPT = {"sgd": 0, "momentum": 1, "adam": 2}
+
+
+class NativeEngine:
+    name = "native-sm100a"
+
+    def __init__(self, spec: ModelSpec, cfg: TrainConfig, comm: Communicator, device: torch.device,
+                 conv_impl: str = "auto"):
+        if device.type != "cuda":
+            raise RuntimeError("NativeEngine needs a CUDA device")
+        N.lib()                                   # fail loudly if the extension is missing
+        self.spec, self.cfg, self.comm, self.device = spec, cfg, comm, device
+        torch.cuda.set_device(device)
+        self.B = cfg.batch
+        self.n = flat_size(spec)
+        self.p2p = comm if getattr(comm, "backend", "") == "p2p" else None
+        self.world = comm.size if self.p2p is not None else 1
+        self.conv_impl = conv_impl
+        # the fused step is valid only when K1 itself reaches every rank of the world
+        self.can_fuse = comm.size == 1 or self.p2p is not None
+        if spec.image_size != 28 or spec.c1 % 32 or spec.c2 % 8 or spec.fc % 8:
+            raise ValueError("NativeEngine supports 28x28 inputs, c1 % 32 == 0, c2 % 8 == 0, fc % 8 == 0")
+        self._alloc_state()
+        self._alloc_activations(max(self.B, cfg.eval_batch))
+        self.init_params(cfg.seed)
+        self.opt_step = 0
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graph_key = None
+        self.data_x = self.data_y = None
+        self.rows = 0
+        self.decay_rows = cfg.lr_decay_rows
+        self._side = torch.cuda.Stream(device=device)
+        self.last_aux: Dict = {}
+
+    # ------------------------------------------------------------------ buffers
+    def _sym(self, nbytes: int):
+        """Symmetric (peer-mapped) allocation under p2p, plain device memory otherwise."""
+        if self.p2p is not None:
+            sb = self.p2p.alloc_symmetric(nbytes)
+            return sb.local, sb.ptrs
+        t = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+        return t, [t.data_ptr()]
+
+    def _alloc_state(self):
+        n, dev = self.n, self.device
+        raw, self._param_ptrs = self._sym(n * 4)
+        self.flat_params = raw.view(torch.float32)
+        raw, self._grad_ptrs = self._sym(n * 4)
+        self.flat_grads = raw.view(torch.float32)
+        raw, self._shadow_ptrs = self._sym(n * 2)
+        self.shadow = raw.view(torch.bfloat16)
+        self.slots: List[torch.Tensor] = []
+        if self.cfg.optimizer in ("momentum", "adam"):
+            self.slots.append(torch.zeros(n, device=dev))
+        if self.cfg.optimizer == "adam":
+            self.slots.append(torch.zeros(n, device=dev))
+        self.dev_step = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.loss_acc = torch.zeros(1, device=dev)
+        self.err_acc = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._seq = torch.zeros(256, dtype=torch.int32, device=dev)
+        self._status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.P = {p.key: self.flat_params[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
+        self.G = {p.key: self.flat_grads[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
+        self.S = {p.key: self.shadow[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
+        # ranges that must start each step at zero because their wgrad kernels accumulate
+        fc1w = self.spec.param("fc1_weight")
+        c2w = self.spec.param("conv2_weight")
+        self._zero_ranges = [(0, c2w.offset), (c2w.offset + c2w.numel, fc1w.offset),
+                             (fc1w.offset + fc1w.numel, n)]
+
+    def _alloc_activations(self, Bmax: int):
+        s, dev = self.spec, self.device
+        bf, f32 = torch.bfloat16, torch.float32
+        z = lambda *shape, dtype=bf: torch.zeros(*shape, dtype=dtype, device=dev)  # noqa: E731
+        self.Bmax = Bmax
+        self.x_in = z(Bmax, 784, dtype=f32)
+        self.y_in = z(Bmax, dtype=torch.int32)
+        self.a1p, self.idx1 = z(Bmax, 14, 14, s.c1), z(Bmax, 14, 14, s.c1, dtype=torch.uint8)
+        self.a2p, self.idx2 = z(Bmax, 7, 7, s.c2), z(Bmax, 7, 7, s.c2, dtype=torch.uint8)
+        self.h = z(Bmax, s.fc)
+        self.logits, self.probs = z(Bmax, s.num_classes, dtype=f32), z(Bmax, s.num_classes, dtype=f32)
+        self.dlogits = z(Bmax, s.num_classes, dtype=f32)
+        self.dh, self.dflat = z(Bmax, s.fc), z(Bmax, s.flat_dim)
+        self.da2 = z(Bmax, 14, 14, s.c2)
+        self.dp1 = z(Bmax, 14, 14, s.c1)
+        # generic (im2col) convolution path
+        self.col = z(Bmax * 196, 25 * s.c1)
+        self.a2 = z(Bmax * 196, s.c2)
+        self.dcol = z(Bmax * 196, 25 * s.c1)
+        # split-K scratch for the conv2 weight gradient (K = B*196 is the long axis)
+        self.wg_splits = 16
+        ws, cn = N.gemm_scratch_sizes(25 * s.c1, s.c2, 64, self.wg_splits)
+        self.wg_ws = torch.zeros(max(ws, 16), dtype=torch.uint8, device=dev)
+        self.wg_cnt = torch.zeros(max(cn, 16), dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ parameters
+    def init_params(self, seed: int):
+        """Seeded init, identical on every rank (``mpipy.py:38-53``), on the device (K10)."""
+        for i, p in enumerate(self.spec.params):
+            dst = self.flat_params[p.offset:p.offset + p.numel]
+            if p.init == "trunc_normal":
+                N.call("mtb_init_trunc_normal", dst.data_ptr(), p.numel, p.init_value, seed, i)
+            else:
+                N.call("mtb_fill_f32", dst.data_ptr(), p.numel, p.init_value if p.init == "const" else 0.0)
+        self.params_changed()
+
+    def params_changed(self):
+        """Refresh the bf16 shadow after the fp32 master was written from outside K1."""
+        N.call("mtb_cast_f32_to_bf16", self.flat_params.data_ptr(), self.shadow.data_ptr(), self.n)
+
+    def synchronize(self):
+        torch.cuda.current_stream().synchronize()
+
+    def get_params(self):
+        self.synchronize()
+        return {k: v.detach().cpu().numpy().copy() for k, v in self.P.items()}
+
+    def get_slots(self):
+        self.synchronize()
+        names = ["m", "v"]
+        return {p.key: {names[i]: s[p.offset:p.offset + p.numel].view(p.shape).cpu().numpy().copy()
+                        for i, s in enumerate(self.slots)} for p in self.spec.params}
+
+    def set_state(self, params, slots, step: int):
+        names = ["m", "v"]
+        for p in self.spec.params:
+            self.P[p.key].copy_(torch.from_numpy(np.asarray(params[p.key], dtype=np.float32).reshape(p.shape)))
+            for i, s in enumerate(self.slots):
+                if slots and p.key in slots and names[i] in slots[p.key]:
+                    s[p.offset:p.offset + p.numel].copy_(
+                        torch.from_numpy(np.asarray(slots[p.key][names[i]], dtype=np.float32).reshape(-1)))
+        self.dev_step.fill_(step)
+        self.opt_step = step
+        self.params_changed()
+        self.synchronize()
+
+    # ------------------------------------------------------------------ data
+    def attach_dataset(self, shards):
+        """Keep this rank's train shard resident in HBM (fp32 [rows,784] + int32 labels): the
+        reference re-feeds every batch from host memory (``mpipy.py:83-85``)."""
+        x = torch.from_numpy(np.ascontiguousarray(shards.train_x.reshape(shards.train_x.shape[0], -1)))
+        self.data_x = x.to(self.device, dtype=torch.float32)
+        self.data_y = torch.from_numpy(np.ascontiguousarray(shards.train_y)).to(self.device, dtype=torch.int32)
+        self.rows = self.data_x.shape[0]
+        if not self.decay_rows:
+            self.decay_rows = self.rows
+
+    def attach_device_dataset(self, x: torch.Tensor, y: torch.Tensor):
+        self.data_x, self.data_y, self.rows = x, y, x.shape[0]
+        if not self.decay_rows:
+            self.decay_rows = self.rows
+
+    def resident_batch(self, sampler, step: int):
+        return None, None                       # fused_step pulls the window on the device
+
+    def stage_batch(self, images, labels):
+        """Copy a caller-supplied batch into the static input buffers (H2D if on the host)."""
+        B = self.B
+        if isinstance(images, np.ndarray):
+            images = torch.from_numpy(images)
+        if isinstance(labels, np.ndarray):
+            labels = torch.from_numpy(labels)
+        self.x_in[:B].copy_(images.reshape(B, -1), non_blocking=True)
+        self.y_in[:B].copy_(labels.reshape(B), non_blocking=True)
+
+    # ------------------------------------------------------------------ forward
+    def _forward(self, B: int, train: bool, with_loss: bool):
+        s, c = self.spec, self.cfg
+        P, S = self.P, self.S
+        keep = s.keep_prob if (train and c.dropout) else 1.0
+        # conv1 + bias + ReLU + pool (mpipy.py:156-158)
+        N.call("mtb_conv1_fwd", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
+               self.a1p.data_ptr(), self.idx1.data_ptr(), B, s.c1)
+        # conv2 + bias + ReLU (mpipy.py:159-160) as im2col + tcgen05 GEMM, then pool (mpipy.py:161)
+        M2, K2 = B * 196, 25 * s.c1
+        N.call("mtb_im2col_5x5", self.a1p.data_ptr(), self.col.data_ptr(), B, 14, 14, s.c1)
+        N.gemm_bf16(self.col, S["conv2_weight"].view(K2, s.c2), self.a2, M2, s.c2, K2, False, True,
+                    bias=P["conv2_bias"], relu=True)
+        N.call("mtb_maxpool2x2_fwd", self.a2.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B, 14, 14, s.c2)
+        # FC1 + bias + ReLU + dropout in the GEMM epilogue (mpipy.py:165-166)
+        flat = self.a2p.view(self.Bmax, s.flat_dim)
+        N.gemm_bf16(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
+                    keep_prob=keep, seed=c.seed, step_ptr=self.dev_step,
+                    bn=64 if B * s.fc < 96 * 128 * 128 else 128)
+        # FC2 + softmax + CE + dlogits (mpipy.py:167, :55-56, :67)
+        N.call("mtb_fc2_softmax_ce", self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
+               self.y_in.data_ptr() if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
+               self.dlogits.data_ptr() if with_loss else None, self.loss_acc.data_ptr() if with_loss else None,
+               self.err_acc.data_ptr() if with_loss else None, B, s.fc, s.num_classes)
+
+    # ------------------------------------------------------------------ backward
+    def _backward(self, B: int):
+        s, c = self.spec, self.cfg
+        P, S, G = self.P, self.S, self.G
+        scale = 1.0 / s.keep_prob if c.dropout else 1.0
+        M2, K2 = B * 196, 25 * s.c1
+        flat = self.a2p.view(self.Bmax, s.flat_dim)
+        N.call("mtb_fc2_wgrad", self.h.data_ptr(), self.dlogits.data_ptr(), G["fc2_weight"].data_ptr(),
+               G["fc2_bias"].data_ptr(), B, s.fc, s.num_classes)
+        N.call("mtb_fc2_dgrad", self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(), self.h.data_ptr(),
+               self.dh.data_ptr(), B, s.fc, s.num_classes, scale)
+        N.call("mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
+        # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket
+        N.gemm_bf16(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=128)
+        # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand
+        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=128)
+        # pool2 + ReLU backward (O19, O18), conv2 bias gradient
+        N.call("mtb_unpool_relu_bwd", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
+               self.da2.data_ptr(), B, 14, 14, s.c2)
+        da2 = self.da2.view(self.Bmax * 196, s.c2)
+        N.call("mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
+        # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
+        N.gemm_bf16(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
+                    splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
+        # conv2 dgrad: dcol = da2 W2^T, then col2im
+        N.gemm_bf16(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
+        N.call("mtb_col2im_5x5", self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
+        # pool1 + ReLU backward fused into the conv1 weight gradient
+        N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
+               self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
+
+    def _zero_step_accumulators(self):
+        for lo, hi in self._zero_ranges:
+            if hi > lo:
+                self.flat_grads[lo:hi].zero_()
+        self.loss_acc.zero_()
+        self.err_acc.zero_()
+
+    # ------------------------------------------------------------------ update (K1)
+    def _fused_args(self, peers: bool, lr_override: float = -1.0) -> N.FusedArgs:
+        c, s = self.cfg, self.spec
+        if peers and self.p2p is not None:
+            a = self.p2p.fused_args()
+            for r in range(self.world):
+                a.grads[r], a.params[r], a.shadow[r] = self._grad_ptrs[r], self._param_ptrs[r], self._shadow_ptrs[r]
+            a.scale = 1.0 / self.world
+        else:
+            a = N.FusedArgs()
+            a.world, a.rank = 1, 0
+            a.grads[0], a.params[0], a.shadow[0] = (self.flat_grads.data_ptr(), self.flat_params.data_ptr(),
+                                                    self.shadow.data_ptr())
+            a.seq, a.status = self._seq.data_ptr(), self._status.data_ptr()
+            a.scale = 1.0
+        a.optimizer = _OPT[c.optimizer]
+        a.slot_m = self.slots[0].data_ptr() if self.slots else None
+        a.slot_v = self.slots[1].data_ptr() if len(self.slots) > 1 else None
+        a.lr0, a.lr_decay, a.lr_override = c.lr, c.lr_decay, lr_override
+        a.batch, a.decay_rows = c.batch, int(self.decay_rows or 0)
+        a.step_ptr = self.dev_step.data_ptr()
+        a.momentum, a.beta1, a.beta2, a.eps, a.wd = c.momentum, c.beta1, c.beta2, c.adam_eps, c.weight_decay
+        dec = [p for p in s.params if p.decay]
+        a.n_ranges = len(dec) if c.weight_decay else 0
+        for i, p in enumerate(dec):
+            a.range_begin[i], a.range_end[i] = p.offset, p.offset + p.numel
+        return a
+
+    def _pick_algo(self, count: int) -> int:
+        algo = self.cfg.comm_algo
+        if self.world == 1 or algo == "oneshot":
+            return 0
+        if algo == "twoshot":
+            return 1
+        return 1 if count * 4 > (256 << 10) else 0
+
+    def _update(self, peers: bool, lr_override: float = -1.0):
+        a = self._fused_args(peers, lr_override)
+        a.offset, a.count = 0, self.n
+        a.algo = self._pick_algo(self.n) if peers else 0
+        N.call("mtb_fused_allreduce_update", C.byref(a))
+        N.call("mtb_advance_step", self.dev_step.data_ptr())
+
+    # ------------------------------------------------------------------ engine interface
+    def compute_grads(self, x, y, step: int) -> float:
+        """Eager forward+backward into ``flat_grads`` (generic path used with non-fused sync modes)."""
+        if x is not None:
+            self.stage_batch(x, y)
+        else:
+            self._window()
+        self._zero_step_accumulators()
+        self._forward(self.B, True, True)
+        self._backward(self.B)
+        return self._read_loss()
+
+    def apply(self, lr: float) -> None:
+        self._update(peers=False, lr_override=float(lr))
+        self.opt_step += 1
+
+    def _window(self):
+        if self.data_x is None:
+            raise RuntimeError("no resident dataset: call attach_dataset() or pass a batch")
+        N.call("mtb_batch_window", self.data_x.data_ptr(), self.data_y.data_ptr(), self.dev_step.data_ptr(),
+               self.rows, self.B, self.x_in.data_ptr(), self.y_in.data_ptr())
+
+    def _read_loss(self) -> float:
+        loss = float(self.loss_acc.item())
+        if self.cfg.weight_decay:
+            l2 = torch.zeros(1, device=self.device)
+            for p in self.spec.params:
+                if p.decay:
+                    N.call("mtb_l2_half_sumsq", self.P[p.key].data_ptr(), p.numel, l2.data_ptr())
+            loss += self.cfg.weight_decay * float(l2.item())
+        return loss
+
+    def _step_body(self):
+        self._zero_step_accumulators()
+        self._forward(self.B, True, True)
+        self._backward(self.B)
+        self._update(peers=True)
+
+    def fused_step(self, images, labels, lr, step: int, read_loss: bool = True):
+        """One full step: (window | staged batch) -> graph replay.  ``lr`` is ignored: the
+        schedule runs on the device from the device step counter."""
+        if images is not None:
+            self.stage_batch(images, labels)
+        else:
+            self._window()
+        if self.cfg.cuda_graph:
+            if self._graph is None:
+                self._capture()
+            self._graph.replay()
+        else:
+            self._step_body()
+        self.opt_step += 1
+        return float(self.loss_acc.item()) if read_loss else 0.0
+
+    def _capture(self):
+        """Warm up eagerly (sets kernel attributes, builds tensor maps), roll the state back, capture."""
+        snap = [t.clone() for t in (self.flat_params, self.shadow, self.dev_step, *self.slots)]
+        if self.p2p is not None:
+            self.p2p.barrier()
+        self._step_body()
+        torch.cuda.synchronize()
+        if self.p2p is not None:
+            self.p2p.barrier()
+        for t, s in zip((self.flat_params, self.shadow, self.dev_step, *self.slots), snap):
+            t.copy_(s)
+        torch.cuda.synchronize()
+        if self.p2p is not None:
+            self.p2p.barrier()
+        g = torch.cuda.CUDAGraph()
+        launches = N.LAUNCHES
+        with torch.cuda.graph(g, stream=self._side):
+            self._step_body()
+        self.launches_per_step = N.LAUNCHES - launches
+        self._graph = g
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ inference
+    def predict(self, x, dropout_step: Optional[int] = None) -> torch.Tensor:
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(x)
+        B = x.shape[0]
+        if B > self.Bmax:
+            raise ValueError(f"batch {B} exceeds the engine's static capacity {self.Bmax}")
+        self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
+        self._forward(B, dropout_step is not None, False)
+        return self.probs[:B].clone()
+
+    def predict_all(self, data, B: int, dropout_step: Optional[int] = None) -> np.ndarray:
+        """``eval_in_batches`` (``mpipy.py:169-183``) with the data uploaded once."""
+        if isinstance(data, np.ndarray):
+            data = torch.from_numpy(data)
+        size = data.shape[0]
+        dev = data.reshape(size, -1).to(self.device, dtype=torch.float32)
+        out = torch.empty(size, self.spec.num_classes, device=self.device)
+        for begin in range(0, size, B):
+            end = begin + B
+            if end <= size:
+                out[begin:end] = self.predict(dev[begin:end], dropout_step)
+            else:
+                out[begin:] = self.predict(dev[-B:], dropout_step)[begin - size:]
+        return out.cpu().numpy()
+
+    def close(self):
+        self._graph = None

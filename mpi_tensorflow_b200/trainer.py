@@ -61,7 +61,7 @@ class Trainer:
         self.sampler = None
         self.decay_rows = cfg.lr_decay_rows
         self._fault = FaultSpec.from_env()
-        self._fused = hasattr(self.engine, "fused_step") and cfg.sync in ("grad_allreduce", "none")
+        self._fused = getattr(self.engine, "can_fuse", False) and cfg.sync in ("grad_allreduce", "none")
         if cfg.resume:
             self.load_checkpoint(cfg.resume)
 
