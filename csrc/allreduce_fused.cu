@@ -34,7 +34,7 @@ using namespace mtb;
 constexpr int kMaxRanks = 16;
 constexpr int kMaxBlocks = 256;
 constexpr int kMaxRanges = 8;
-constexpr long long kSpinLimit = 6000000000ll;      // ~3 s
+constexpr long long kSpinLimit = 30000000000ll;     // ~15 s at 2 GHz
 
 struct FusedParams {
   int world, rank, algo, optimizer;                 // optimizer: -1 none (plain allreduce), 0 sgd, 1 momentum, 2 adam

@@ -100,7 +100,12 @@ class P2PComm(Communicator):
             raise CommTimeout(f"rank {self.rank}: a device-side wait on a peer timed out (code {code})")
 
     def barrier(self) -> None:
+        """Host-level barrier.  Ranks first meet on the bootstrap channel (which may take as
+        long as the slowest rank needs), then on the device flags, so the bounded device-side
+        spin only ever covers launch skew."""
         if self.size > 1:
+            torch.cuda.current_stream().synchronize()
+            self.boot.barrier()
             a = self.fused_args()
             N.call("mtb_p2p_barrier", C.byref(a))
         torch.cuda.current_stream().synchronize()

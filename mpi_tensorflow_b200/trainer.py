@@ -96,6 +96,15 @@ class Trainer:
             self.engine.attach_dataset(shards)
         return shards
 
+    def attach_device_dataset(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        """Use a shard that already lives in device memory (``[rows,784]`` fp32 + int32 labels):
+        ``step()`` without arguments then walks it with the reference's sequential window
+        (``mpipy.py:80-82``) entirely on the device."""
+        self.engine.attach_device_dataset(images, labels)
+        self.sampler = D.SequentialSampler(images.shape[0], self.cfg.batch)
+        if not self.decay_rows:
+            self.decay_rows = images.shape[0]
+
     # ------------------------------------------------------------------ step
     def lr_at(self, step: int) -> float:
         c = self.cfg
@@ -103,11 +112,13 @@ class Trainer:
             return c.lr
         return learning_rate(step, c.batch, self.decay_rows, c.lr, c.lr_decay)          # mpipy.py:60-64
 
-    def step(self, images=None, labels=None) -> float:
+    def step(self, images=None, labels=None, read_loss: bool = True) -> float:
         """One optimizer step.  With ``images``/``labels`` (host or device
         tensors, NHWC float and int labels) the batch is copied to the device as
         needed; without, the next window of the resident shard is used
-        (``mpipy.py:80-85``).  Returns the loss of this step as a float."""
+        (``mpipy.py:80-85``).  Returns the loss of this step as a float; with
+        ``read_loss=False`` the fused GPU path skips the device-to-host read (and
+        the host sync it implies) and returns 0.0."""
         step = self.global_step
         maybe_inject(self._fault, self.comm.rank, step)
         lr = self.lr_at(step)
@@ -120,7 +131,7 @@ class Trainer:
                 idx = self.sampler.indices(step)
                 images, labels = self.shards.train_x[idx], self.shards.train_y[idx]
         if self._fused:
-            loss = self.engine.fused_step(images, labels, lr, step)
+            loss = self.engine.fused_step(images, labels, lr, step, read_loss=read_loss)
         else:
             with self.timer.phase("fwd_bwd"):
                 loss = self.engine.compute_grads(images, labels, step)

@@ -1,0 +1,104 @@
+"""End-to-end checks of the GPU engine on one B200: one step against the
+bf16-emulating CPU oracle, loss going down, CUDA-graph replay == eager, checkpoint
+round trip through the device, and the public Trainer API with host batches."""
+import numpy as np
+import pytest
+import torch
+
+from mpi_tensorflow_b200 import TrainConfig, Trainer
+from mpi_tensorflow_b200.models.oracle import Oracle, dropout_keep_mask
+from mpi_tensorflow_b200.models.spec import get_spec
+from mpi_tensorflow_b200.utils import data as D
+
+pytestmark = pytest.mark.gpu
+
+
+def _shards(n_rows, seed=0):
+    u8, lab = D.synthetic_mnist(n_rows, seed)
+    x = D.normalize_u8(u8).reshape(n_rows, 28, 28, 1)
+    y = lab.astype(np.int64)
+    return D.Shards(x, y, x[:128], y[:128], x[:64], y[:64])
+
+
+def _cfg(**kw):
+    base = dict(model="tutorial512", batch=64, eval_every=0, log_every=0, dropout=False, weight_decay=5e-4)
+    base.update(kw)
+    return TrainConfig(**base)
+
+
+@pytest.mark.parametrize("model,batch,dropout", [("tutorial512", 64, False), ("official1024", 100, True)])
+def test_one_step_grads_match_bf16_oracle(model, batch, dropout):
+    cfg = _cfg(model=model, batch=batch, dropout=dropout, cuda_graph=False)
+    tr = Trainer(cfg, device=torch.device("cuda", 0))
+    sh = _shards(512)
+    tr.load_data(sh)
+    eng = tr.engine
+    spec = get_spec(model)
+    p0 = {k: torch.from_numpy(v) for k, v in eng.get_params().items()}
+    loss = eng.compute_grads(None, None, 0)
+    grads = eng.flat_grads.cpu()
+    orc = Oracle(spec, params=p0, weight_decay=0.0, emulate_bf16=True)
+    mask = dropout_keep_mask(spec, batch, cfg.seed, 0) if dropout else None
+    x = torch.from_numpy(sh.train_x[:batch])
+    y = torch.from_numpy(sh.train_y[:batch])
+    rloss, rg, aux = orc.loss_and_grads(x, y, mask)
+    l2 = sum(0.5 * float((p0[p.key] ** 2).sum()) for p in spec.params if p.decay)
+    assert abs(loss - (rloss + cfg.weight_decay * l2)) < 2e-2 * max(1.0, abs(rloss))
+    for p in spec.params:
+        g = grads[p.offset:p.offset + p.numel]
+        r = rg[p.key].reshape(-1)
+        rel = float((g - r).norm() / (r.norm() + 1e-12))
+        # conv1 runs on fp32 inputs/weights on the device while the oracle rounds them to bf16,
+        # and its gradient sits at the end of the longest bf16 chain
+        tol = 6e-2 if p.layer == "conv1" else 3e-2
+        assert rel < tol, f"{p.key}: rel err {rel}"
+
+
+def test_training_reduces_loss_and_graph_matches_eager():
+    sh = _shards(1024)
+    runs = {}
+    for graph in (False, True):
+        tr = Trainer(_cfg(batch=64, lr=0.02, cuda_graph=graph, dropout=True), device=torch.device("cuda", 0))
+        tr.load_data(sh)
+        losses = [tr.step() for _ in range(40)]
+        runs[graph] = (losses, tr.engine.flat_params.clone())
+        assert losses[-1] < 0.7 * losses[0], losses
+        err = tr.evaluate("test")
+        assert 0.0 <= err <= 100.0
+        tr.close()
+    # atomics in the small wgrad kernels reorder fp32 sums and bf16 rounding amplifies that
+    # over 40 steps, so "equal" means close
+    a, b = runs[False][1], runs[True][1]
+    assert float((a - b).norm() / a.norm()) < 2e-2
+    assert abs(runs[False][0][-1] - runs[True][0][-1]) < 0.1
+
+
+def test_public_api_host_batches_and_checkpoint(tmp_path):
+    dev = torch.device("cuda", 0)
+    cfg = _cfg(model="official1024", batch=100, optimizer="adam", lr=1e-3, lr_decay=1.0, dropout=True)
+    tr = Trainer(cfg, device=dev)
+    sh = _shards(400)
+    x = torch.from_numpy(sh.train_x).pin_memory()
+    y = torch.from_numpy(sh.train_y.astype(np.int32)).pin_memory()
+    losses = [tr.step(x[(i % 4) * 100:(i % 4 + 1) * 100], y[(i % 4) * 100:(i % 4 + 1) * 100]) for i in range(24)]
+    assert np.isfinite(losses).all() and losses[-1] < losses[0]
+    path = str(tmp_path / "model.ckpt")
+    tr.save_checkpoint(path)
+    before = tr.engine.get_params()
+    tr2 = Trainer(cfg, device=dev)
+    tr2.load_checkpoint(path)
+    after = tr2.engine.get_params()
+    for k in before:
+        assert np.array_equal(before[k], after[k])
+    assert tr2.global_step == 24
+    p1 = tr.engine.predict(x[:64]).cpu()
+    p2 = tr2.engine.predict(x[:64]).cpu()
+    assert torch.allclose(p1, p2, atol=1e-6)
+    assert torch.allclose(p1.sum(1), torch.ones(64), atol=1e-4)
+
+
+def test_wide_preset_runs():
+    tr = Trainer(_cfg(model="wide", batch=32, optimizer="adam", lr=1e-4, lr_decay=1.0), device=torch.device("cuda", 0))
+    tr.load_data(_shards(256))
+    losses = [tr.step() for _ in range(6)]
+    assert np.isfinite(losses).all()

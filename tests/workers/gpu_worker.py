@@ -1,0 +1,138 @@
+"""Per-rank body of the multi-GPU tests (one process per GPU, launched by parallel.launch).
+
+modes:
+  algebra   every P2PComm collective on device tensors equals serial NumPy
+  fused     the fused allreduce+update kernel: replicas bit-identical, one-shot == two-shot,
+            N ranks x batch b == 1 rank x batch N*b (DP equivalence)
+  train     Trainer.fit() through the public API, CUDA graph on
+"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+from mpi_tensorflow_b200 import TrainConfig, Trainer  # noqa: E402
+from mpi_tensorflow_b200.parallel import world  # noqa: E402
+from mpi_tensorflow_b200.utils import data as D  # noqa: E402
+
+
+def shards_for(rank, rows, seed=0):
+    u8, lab = D.synthetic_mnist(rows, seed, offset=rank * rows)
+    x = D.normalize_u8(u8).reshape(rows, 28, 28, 1)
+    y = lab.astype(np.int64)
+    return D.Shards(x, y, x[:64], y[:64], x[:64], y[:64])
+
+
+def algebra(comm):
+    r, n, dev = comm.rank, comm.size, comm.device
+    rng = np.random.default_rng(99)
+    for count in (4, 1000, 100003, (3 << 20) + 1):
+        full = rng.standard_normal((n, count)).astype(np.float32)
+        t = torch.from_numpy(full[r].copy()).to(dev)
+        comm.allreduce(t, average=True)
+        ref = full[0].copy()
+        for p in range(1, n):
+            ref += full[p]
+        ref *= np.float32(1.0 / n)
+        assert np.allclose(t.cpu().numpy(), ref, rtol=1e-6, atol=1e-6), ("allreduce", count)
+        chk = t.clone()
+        comm.bcast(chk, root=0)
+        assert torch.equal(chk, t), "allreduce result differs across ranks"
+        recv = torch.zeros(count, device=dev)
+        comm.scatter(torch.from_numpy(full.copy()) if r == 0 else None, recv, root=0)
+        assert np.array_equal(recv.cpu().numpy(), full[r]), ("scatter", count)
+        out = torch.zeros(n, count, device=dev) if r == 0 else None
+        comm.gather(torch.from_numpy(full[r].copy()).to(dev), out, root=0)
+        if r == 0:
+            assert np.array_equal(out.cpu().numpy(), full), ("gather", count)
+        ag = torch.zeros(n * count, device=dev)
+        comm.allgather(torch.from_numpy(full[r].copy()).to(dev), ag)
+        assert np.array_equal(ag.cpu().numpy().reshape(n, count), full), ("allgather", count)
+        b = torch.from_numpy(full[n - 1].copy()).to(dev) if r == n - 1 else torch.zeros(count, device=dev)
+        comm.bcast(b, root=n - 1)
+        assert np.array_equal(b.cpu().numpy(), full[n - 1]), ("bcast", count)
+    for _ in range(50):
+        comm.barrier()
+    print(f"GPU_COMM_OK rank {r}/{n}", flush=True)
+
+
+def fused(comm, outdir):
+    r, n, dev = comm.rank, comm.size, comm.device
+    b, steps = 32, 6
+    finals = {}
+    for algo in ("oneshot", "twoshot"):
+        cfg = TrainConfig(model="tutorial512", batch=b, eval_every=0, log_every=0, dropout=False,
+                          comm_algo=algo, cuda_graph=(algo == "twoshot"), lr_decay_rows=10 ** 9)
+        tr = Trainer(cfg, comm)
+        # rank r trains on rows [r*b, (r+1)*b) of every global batch of n*b rows
+        rows = steps * b + b
+        u8, lab = D.synthetic_mnist(n * rows, 5)
+        gx = D.normalize_u8(u8).reshape(n * rows, 28, 28, 1)
+        gy = lab.astype(np.int64)
+        losses = []
+        for s in range(steps):
+            lo = s * n * b + r * b
+            losses.append(tr.step(torch.from_numpy(gx[lo:lo + b]), torch.from_numpy(gy[lo:lo + b]).int()))
+        tr.engine.synchronize()
+        comm.check_status()
+        mine = tr.engine.flat_params.clone()
+        ref = mine.clone()
+        comm.bcast(ref, root=0)
+        assert torch.equal(mine, ref), f"{algo}: replicas diverged"
+        assert torch.equal(tr.engine.shadow, tr.engine.flat_params.to(torch.bfloat16)), "bf16 shadow stale"
+        finals[algo] = mine.cpu()
+        if r == 0 and algo == "oneshot":
+            # single-process big-batch run on the same rows (no peers: world-1 engine)
+            from mpi_tensorflow_b200.parallel.comm import SelfComm
+            cfg1 = TrainConfig(model="tutorial512", batch=n * b, eval_every=0, log_every=0, dropout=False,
+                               cuda_graph=False, lr_decay_rows=10 ** 9)
+            t1 = Trainer(cfg1, SelfComm(), device=dev)
+            for s in range(steps):
+                lo = s * n * b
+                t1.step(torch.from_numpy(gx[lo:lo + n * b]), torch.from_numpy(gy[lo:lo + n * b]).int())
+            t1.engine.synchronize()
+            big = t1.engine.flat_params.cpu()
+            rel = float((big - finals[algo]).norm() / big.norm())
+            assert rel < 2e-3, f"DP equivalence: rel diff {rel}"
+            t1.close()
+        tr.close()
+        comm.barrier()
+    rel = float((finals["oneshot"] - finals["twoshot"]).norm() / finals["oneshot"].norm())
+    assert rel < 1e-3, f"oneshot vs twoshot: {rel}"
+    print(f"GPU_FUSED_OK rank {r}/{n}", flush=True)
+
+
+def train(comm, outdir):
+    cfg = TrainConfig(model="official1024", batch=100, max_steps=30, eval_every=0, log_every=10,
+                      dropout=True, step_timeout_s=60)
+    tr = Trainer(cfg, comm)
+    tr.load_data()
+    res = tr.fit()
+    mine = tr.engine.flat_params.clone()
+    ref = mine.clone()
+    comm.bcast(ref, root=0)
+    assert torch.equal(mine, ref), "replicas diverged"
+    if comm.rank == 0:
+        with open(os.path.join(outdir, "result.json"), "w") as f:
+            json.dump({k: v for k, v in res.items() if k != "phases_ms"}, f)
+    print(f"GPU_TRAIN_OK rank {comm.rank}/{comm.size}", flush=True)
+    tr.close()
+
+
+def main():
+    mode, outdir = sys.argv[1], sys.argv[2]
+    comm = world.init("p2p", "cuda", timeout_s=60)
+    if mode == "algebra":
+        algebra(comm)
+    elif mode == "fused":
+        fused(comm, outdir)
+    elif mode == "train":
+        train(comm, outdir)
+    world.finalize()
+
+
+if __name__ == "__main__":
+    main()
