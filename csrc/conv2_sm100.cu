@@ -1,0 +1,602 @@
+// Second convolution layer (5x5, SAME, 32 -> 64 channels on 14x14 maps; mpipy.py:159-161 and the
+// Conv2DBackpropInput / Conv2DBackpropFilter / MaxPoolGrad ops autodiff adds)
+// as implicit GEMM on tcgen05 with NO im2col anywhere, not even in shared memory.
+//
+// "Shift-GEMM": TMA drops one zero-padded 18x18 halo patch of an image into shared memory
+// (out-of-bounds box coordinates supply the SAME padding), pixels as rows, channels contiguous,
+// hardware-swizzled.  If output pixel (h,w) is GEMM row m = 18h + w, then filter tap (kh,kw)
+// reads patch row m + 18kh + kw: every tap is the SAME patch viewed from a start address moved
+// by whole rows.  tcgen05 shared-memory descriptors swizzle on absolute address bits (pinned by
+// csrc/debug_shift.cu and its test), so the 25 taps are 25 descriptor start addresses and the
+// patch crosses L2 -> SM once instead of 25 times.  4 of every 18 GEMM rows are halo columns
+// whose results are dropped: 1.3x spare MMA work, which is not the bottleneck.
+//
+//   fprop   D[pixel, co]   = sum_tap patch_x [pixel + shift(tap)] . W[tap]      A K-major SW64, B MN-major SW128
+//           epilogue: + bias, ReLU, 2x2 max-pool + argmax through a shared staging tile;
+//           the un-pooled activation never exists in global memory.
+//   dgrad   D[pixel, ci]   = sum_tap patch_dy[pixel + shift(tap)] . W[24-tap]^T A K-major SW128, B K-major SW128
+//   wgrad   D[co, (kw,ci)] = sum_pixel dy[pixel] . patch_x[pixel + 18kh + kw]   both operands MN-major, K = pixels.
+//           One MMA covers all five kw taps: the five B "atoms" are the patch one row apart
+//           (leading-dimension byte offset = one 64-byte row).  Two kh taps share one MMA: the
+//           A operand's second 64-lane atom is dy itself, the first is dy moved back by 36 rows,
+//           i.e. tap kh+2.  Three N=160 MMAs per 16 pixels give all 25 taps in 480 TMEM columns.
+//           Per-CTA partial sums go to a workspace and a second kernel adds them in CTA order
+//           (deterministic); the bias gradient is summed from the same shared tile.
+//
+// All three are persistent, warp-specialised kernels (TMA warp, MMA warp, 4 epilogue warps) with
+// mbarrier rings, one CTA per SM, weights resident in shared memory for the CTA's lifetime.
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "common.cuh"
+#include "sm100.cuh"
+#include "tma_host.cuh"
+
+namespace {
+
+using namespace sm100;
+using bf16 = __nv_bfloat16;
+
+constexpr int HW = 14;                 // feature map is 14 x 14
+constexpr int PWID = 18;               // padded width = 14 + 2*2
+constexpr int CIN = 32, COUT = 64, TAPS = 25;
+constexpr int kThreads = 192;
+constexpr int M_ROWS = HW * PWID;      // 252 GEMM rows per image (incl. 4 halo columns per row)
+constexpr int PATCH_ROWS = PWID * PWID;  // 324
+constexpr int W_BYTES = TAPS * CIN * COUT * 2;      // 102400: every tap's [32 ci][64 co] tile
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// ======================================================================================= fprop
+namespace fp {
+constexpr int kStages = 3;
+constexpr int kPatchBytes = 336 * 64;                      // 324 rows land, slack keeps tile 1's taps in bounds
+constexpr int kOffW = 0;
+constexpr int kOffPatch = W_BYTES;
+constexpr int kOffStage = kOffPatch + kStages * kPatchBytes;   // bf16 [256][64] relu'd tile for pooling
+constexpr int kOffBar = kOffStage + 256 * 128;
+constexpr int kSmem = 1024 + kOffBar + 128;
+}  // namespace fp
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                        const float* __restrict__ bias, bf16* __restrict__ out, uint8_t* __restrict__ idx, int B) {
+  using namespace fp;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem + kOffW;
+  uint8_t* sPatch = smem + kOffPatch;
+  uint8_t* sStage = smem + kOffStage;
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* p_full = w_full + 1;
+  uint64_t* p_empty = p_full + kStages;
+  uint64_t* a_full = p_empty + kStages;
+  uint64_t* a_empty = a_full + 2;
+  uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_x);
+    tma_prefetch_desc(&map_w);
+    mbar_init(w_full, 1);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], 1); mbar_init(&p_empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<256>(holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(w_full, W_BYTES);
+      for (int t = 0; t < TAPS; ++t) tma_load_2d(sW + t * 4096, &map_w, w_full, 0, t * CIN);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        mbar_wait(&p_empty[s], ph ^ 1);
+        mbar_arrive_expect_tx(&p_full[s], PATCH_ROWS * 64);
+        tma_load_4d(sPatch + s * kPatchBytes, &map_x, &p_full[s], 0, -2, -2, img);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, COUT, false, true);
+      mbar_wait(w_full, 0);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        const int a = it & 1, aph = (it >> 1) & 1;
+        mbar_wait(&p_full[s], ph);
+        mbar_wait(&a_empty[a], aph ^ 1);
+        tc_fence_after();
+        const uint32_t pbase = smem_u32(sPatch + s * kPatchBytes);
+        const uint32_t wbase = smem_u32(sW);
+#pragma unroll 1
+        for (int tile = 0; tile < 2; ++tile) {
+          const uint32_t d = tmem + a * 128 + tile * 64;
+#pragma unroll 1
+          for (int tap = 0; tap < TAPS; ++tap) {
+            const int shift = (tap / 5) * PWID + (tap % 5);
+            const uint32_t arow = pbase + (uint32_t)(tile * 128 + shift) * 64;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const uint64_t da = make_smem_desc(arow + k * 32, 16, 512, kSwizzle64B);
+              const uint64_t db = make_smem_desc(wbase + tap * 4096 + k * 2048, 4096, 1024, kSwizzle128B);
+              mma_f16(d, da, db, idesc, (tap | k) != 0);
+            }
+          }
+        }
+        mma_commit(&p_empty[s]);
+        mma_commit(&a_full[a]);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;
+    const int t128 = q * 32 + lane;                 // 0..127: TMEM lane = row within a tile
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int a = it & 1, aph = (it >> 1) & 1;
+      mbar_wait(&a_full[a], aph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int tile = 0; tile < 2; ++tile) {
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + a * 128 + tile * 64;
+        const int row = tile * 128 + t128;
+        uint8_t* dst = sStage + row * 128;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              v[e] = fmaxf(__uint_as_float(r[8 * j + e]) + __ldg(bias + c * 32 + 8 * j + e), 0.f);
+            uint4 pk;
+            pk.x = mtb::pack_bf16x2(v[0], v[1]); pk.y = mtb::pack_bf16x2(v[2], v[3]);
+            pk.z = mtb::pack_bf16x2(v[4], v[5]); pk.w = mtb::pack_bf16x2(v[6], v[7]);
+            const int chunk = c * 4 + j;
+            *reinterpret_cast<uint4*>(dst + ((chunk ^ (row & 7)) << 4)) = pk;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_empty[a]);
+      epi_bar();                                     // staging tile complete
+      // 2x2 max-pool + argmax (first max wins, order (0,0),(0,1),(1,0),(1,1))
+      for (int item = t128; item < 49 * 8; item += 128) {
+        const int pp = item >> 3, chunk = item & 7;
+        const int ph = pp / 7, pw = pp % 7;
+        const int m00 = (2 * ph) * PWID + 2 * pw;
+        float best[8];
+        uint32_t arg[8];
+#pragma unroll
+        for (int pos = 0; pos < 4; ++pos) {
+          const int row = m00 + (pos >> 1) * PWID + (pos & 1);
+          const uint4 pk = *reinterpret_cast<const uint4*>(sStage + row * 128 + ((chunk ^ (row & 7)) << 4));
+          const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = mtb::unpack_bf16x2(w4[e]);
+            if (pos == 0 || f.x > best[2 * e]) { best[2 * e] = f.x; arg[2 * e] = pos; }
+            if (pos == 0 || f.y > best[2 * e + 1]) { best[2 * e + 1] = f.y; arg[2 * e + 1] = pos; }
+          }
+        }
+        uint4 o;
+        o.x = mtb::pack_bf16x2(best[0], best[1]); o.y = mtb::pack_bf16x2(best[2], best[3]);
+        o.z = mtb::pack_bf16x2(best[4], best[5]); o.w = mtb::pack_bf16x2(best[6], best[7]);
+        const size_t off = ((size_t)img * 49 + pp) * COUT + chunk * 8;
+        *reinterpret_cast<uint4*>(out + off) = o;
+        uint2 k2;
+        k2.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+        k2.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+        *reinterpret_cast<uint2*>(idx + off) = k2;
+      }
+      epi_bar();                                     // staging tile free for the next image
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc<256>(tmem); }
+}
+
+// ======================================================================================= dgrad
+namespace dg {
+constexpr int kStages = 2;
+constexpr int kPatchBytes = 336 * 128;
+constexpr int kOffW = 0;
+constexpr int kOffPatch = W_BYTES;
+constexpr int kOffBar = kOffPatch + kStages * kPatchBytes;
+constexpr int kSmem = 1024 + kOffBar + 128;
+}  // namespace dg
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_w,
+                   bf16* __restrict__ dx, int B) {
+  using namespace dg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem + kOffW;
+  uint8_t* sPatch = smem + kOffPatch;
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* p_full = w_full + 1;
+  uint64_t* p_empty = p_full + kStages;
+  uint64_t* a_full = p_empty + kStages;
+  uint64_t* a_empty = a_full + 2;
+  uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_dy);
+    tma_prefetch_desc(&map_w);
+    mbar_init(w_full, 1);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], 1); mbar_init(&p_empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<128>(holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(w_full, W_BYTES);
+      for (int t = 0; t < TAPS; ++t) tma_load_2d(sW + t * 4096, &map_w, w_full, 0, t * CIN);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        mbar_wait(&p_empty[s], ph ^ 1);
+        mbar_arrive_expect_tx(&p_full[s], PATCH_ROWS * 128);
+        tma_load_4d(sPatch + s * kPatchBytes, &map_dy, &p_full[s], 0, -2, -2, img);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, CIN, false, false);
+      mbar_wait(w_full, 0);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        const int a = it & 1, aph = (it >> 1) & 1;
+        mbar_wait(&p_full[s], ph);
+        mbar_wait(&a_empty[a], aph ^ 1);
+        tc_fence_after();
+        const uint32_t pbase = smem_u32(sPatch + s * kPatchBytes);
+        const uint32_t wbase = smem_u32(sW);
+#pragma unroll 1
+        for (int tile = 0; tile < 2; ++tile) {
+          const uint32_t d = tmem + a * 64 + tile * 32;
+#pragma unroll 1
+          for (int tap = 0; tap < TAPS; ++tap) {      // tap' = flipped tap: weight slot 24 - tap'
+            const int shift = (tap / 5) * PWID + (tap % 5);
+            const uint32_t arow = pbase + (uint32_t)(tile * 128 + shift) * 128;
+            const uint32_t wrow = wbase + (uint32_t)(TAPS - 1 - tap) * 4096;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t da = make_smem_desc(arow + k * 32, 16, 1024, kSwizzle128B);
+              const uint64_t db = make_smem_desc(wrow + k * 32, 16, 1024, kSwizzle128B);
+              mma_f16(d, da, db, idesc, (tap | k) != 0);
+            }
+          }
+        }
+        mma_commit(&p_empty[s]);
+        mma_commit(&a_full[a]);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;
+    const int t128 = q * 32 + lane;
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int a = it & 1, aph = (it >> 1) & 1;
+      mbar_wait(&a_full[a], aph);
+      tc_fence_after();
+      uint32_t r0[32], r1[32];
+      const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + a * 64;
+      tmem_ld_32x32(taddr, r0);
+      tmem_ld_32x32(taddr + 32, r1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_empty[a]);
+#pragma unroll
+      for (int tile = 0; tile < 2; ++tile) {
+        const int m = tile * 128 + t128;
+        const int h = m / PWID, w = m % PWID;
+        if (h < HW && w < HW) {
+          uint4* dst = reinterpret_cast<uint4*>(dx + (((size_t)img * HW + h) * HW + w) * CIN);
+          const uint32_t* r = tile == 0 ? r0 : r1;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 pk;
+            pk.x = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            pk.y = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            pk.z = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            pk.w = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            dst[j] = pk;
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc<128>(tmem); }
+}
+
+// ======================================================================================= wgrad
+namespace wg {
+constexpr int kStages = 3;
+constexpr int kLead = 40;                                  // zero rows in front of dy (36 needed; 40 keeps 1 KiB alignment)
+constexpr int kDyRows = kLead + M_ROWS + 36;               // 328
+constexpr int kDyBytes = kDyRows * 128;                    // 41984
+constexpr int kXRows = 368;                                // 324 land; zero slack up to row 287 + 76
+constexpr int kXBytes = kXRows * 64;                       // 23552
+constexpr int kStageBytes = kDyBytes + kXBytes;            // 65536
+constexpr int kOffBar = kStages * kStageBytes;
+constexpr int kOffRed = kOffBar + 128;                     // fp32 [16][64] bias partials
+constexpr int kSmem = 1024 + kOffRed + 16 * 64 * 4;
+constexpr int kKSteps = 18;                                // 288 pixel rows / 16
+constexpr int kCols = 480;                                 // 3 MMAs x N=160
+constexpr int kPartialFloats = kCols * 128;
+}  // namespace wg
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
+                   float* __restrict__ partial, float* __restrict__ db, int B) {
+  using namespace wg;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* p_full = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* p_empty = p_full + kStages;
+  uint64_t* a_full = p_empty + kStages;
+  uint32_t* holder = reinterpret_cast<uint32_t*>(a_full + 1);
+  float* sRed = reinterpret_cast<float*>(smem + kOffRed);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // guard rows must read as zero (0 * garbage could be NaN): clear everything once, TMA only ever
+  // rewrites the data rows
+  for (int i = threadIdx.x; i < kStages * kStageBytes / 16; i += kThreads)
+    reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&map_x);
+    tma_prefetch_desc(&map_dy);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], 1); mbar_init(&p_empty[s], 5); }
+    mbar_init(a_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+  const int n_img = blockIdx.x < B ? (B - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        mbar_wait(&p_empty[s], ph ^ 1);
+        uint8_t* st = smem + s * kStageBytes;
+        mbar_arrive_expect_tx(&p_full[s], M_ROWS * 128 + PATCH_ROWS * 64);
+        tma_load_4d(st + kLead * 128, &map_dy, &p_full[s], 0, 0, 0, img);
+        tma_load_4d(st + kDyBytes, &map_x, &p_full[s], 0, -2, -2, img);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, 160, true, true);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        mbar_wait(&p_full[s], ph);
+        tc_fence_after();
+        const uint32_t dy0 = smem_u32(smem + s * kStageBytes) + (kLead - 36) * 128;   // row p-36 of dy
+        const uint32_t x0 = smem_u32(smem + s * kStageBytes + kDyBytes);
+#pragma unroll 1
+        for (int ks = 0; ks < kKSteps; ++ks) {
+          const uint64_t da = make_smem_desc(dy0 + ks * 2048, 36 * 128, 1024, kSwizzle128B);
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            const int kh = j == 2 ? 4 : j;
+            const uint64_t db_ = make_smem_desc(x0 + (uint32_t)(ks * 16 + kh * PWID) * 64, 64, 512, kSwizzle64B);
+            mma_f16(tmem + j * 160, da, db_, idesc, (it | ks) != 0);
+          }
+        }
+        mma_commit(&p_empty[s]);
+      }
+      mma_commit(a_full);
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;
+    const int t128 = q * 32 + lane;
+    // ---- bias gradient: column sums of dy straight from the shared tile ----
+    const int chunk = t128 & 7, sub = t128 >> 3;
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int s = it % kStages, ph = (it / kStages) & 1;
+      mbar_wait(&p_full[s], ph);
+      const uint8_t* dy = smem + s * kStageBytes + kLead * 128;
+      for (int r = sub; r < M_ROWS; r += 16) {
+        const uint4 pk = *reinterpret_cast<const uint4*>(dy + r * 128 + ((chunk ^ (r & 7)) << 4));
+        const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = mtb::unpack_bf16x2(w4[e]);
+          acc[2 * e] += f.x;
+          acc[2 * e + 1] += f.y;
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_empty[s]);
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sRed[sub * 64 + chunk * 8 + e] = acc[e];
+    epi_bar();
+    if (t128 < 64 && n_img > 0) {
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) s += sRed[i * 64 + t128];
+      atomicAdd(db + t128, s);
+    }
+    // ---- weight-gradient partial: TMEM -> workspace [col][lane] ----
+    if (n_img > 0) {
+      mbar_wait(a_full, 0);
+      tc_fence_after();
+      float* dst = partial + (size_t)blockIdx.x * kPartialFloats + t128;
+#pragma unroll 1
+      for (int c = 0; c < kCols / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) dst[(size_t)(c * 32 + j) * 128] = __uint_as_float(r[j]);
+      }
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc<512>(tmem); }
+}
+
+// dW[(kh*5+kw)*32+ci][co] = sum over CTAs of partial[cta][j*160 + kw*32 + ci][lane]
+//   kh 0,1,4 -> j 0,1,2, lane 64+co   |   kh 2,3 -> j 0,1, lane co
+__global__ void __launch_bounds__(256)
+conv2_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dW, int n_cta) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= TAPS * CIN * COUT) return;
+  const int co = o % COUT, ci = (o / COUT) % CIN, tap = o / (COUT * CIN);
+  const int kh = tap / 5, kw = tap % 5;
+  int j, lane;
+  if (kh == 2 || kh == 3) { j = kh - 2; lane = co; }
+  else { j = kh == 4 ? 2 : kh; lane = 64 + co; }
+  const float* src = partial + (size_t)(j * 160 + kw * 32 + ci) * 128 + lane;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int c = 0;
+  for (; c + 4 <= n_cta; c += 4) {
+    s0 += __ldcs(src + (size_t)(c + 0) * wg::kPartialFloats);
+    s1 += __ldcs(src + (size_t)(c + 1) * wg::kPartialFloats);
+    s2 += __ldcs(src + (size_t)(c + 2) * wg::kPartialFloats);
+    s3 += __ldcs(src + (size_t)(c + 3) * wg::kPartialFloats);
+  }
+  for (; c < n_cta; ++c) s0 += __ldcs(src + (size_t)c * wg::kPartialFloats);
+  dW[o] = (s0 + s1) + (s2 + s3);
+}
+
+// ---------------------------------------------------------------------------- tensor maps
+struct Key {
+  const void* p; int B; int kind;
+  bool operator<(const Key& o) const { return std::tie(p, B, kind) < std::tie(o.p, o.B, o.kind); }
+};
+std::map<Key, CUtensorMap> g_maps;
+std::mutex g_mu;
+
+// kind 0: x [B,14,14,32] box (32,18,18,1) SW64 | 1: dy [B,14,14,64] box (64,18,18,1) SW128
+// kind 2: dy box (64,18,14,1) SW128            | 3: W [800,64] box (64,32) SW128
+bool get_map(CUtensorMap* out, const void* p, int B, int kind) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  Key k{p, B, kind};
+  auto it = g_maps.find(k);
+  if (it != g_maps.end()) { *out = it->second; return true; }
+  CUtensorMap m;
+  bool ok;
+  if (kind == 3) {
+    uint64_t dims[2] = {COUT, (uint64_t)TAPS * CIN};
+    uint64_t str[1] = {COUT * 2};
+    uint32_t box[2] = {COUT, CIN};
+    ok = tma::make(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  } else {
+    const uint64_t C = kind == 0 ? CIN : COUT;
+    uint64_t dims[4] = {C, HW, HW, (uint64_t)B};
+    uint64_t str[3] = {C * 2, C * 2 * HW, C * 2 * HW * HW};
+    uint32_t box[4] = {(uint32_t)C, PWID, kind == 2 ? (uint32_t)HW : (uint32_t)PWID, 1};
+    ok = tma::make(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, p, dims, str, box,
+                   kind == 0 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
+  }
+  if (!ok) return false;
+  if (g_maps.size() > 1024) g_maps.clear();
+  g_maps[k] = m;
+  *out = m;
+  return true;
+}
+
+template <typename K>
+int set_smem(K kern, int bytes, bool* done) {
+  if (!*done) {
+    MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    *done = true;
+  }
+  return 0;
+}
+
+inline int grid_for(int B) { return B < mtb::kNumSMs ? B : mtb::kNumSMs; }
+
+}  // namespace
+
+extern "C" {
+
+int mtb_conv2_supported(int H, int cin, int cout) { return H == HW && cin == CIN && cout == COUT; }
+
+int mtb_conv2_fprop_pool(const void* x_bf16, const void* w_bf16, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                         cudaStream_t stream) {
+  MTB_REQUIRE(x_bf16 && w_bf16 && bias && out_bf16 && idx && B > 0, "conv2_fprop: bad argument");
+  CUtensorMap mx, mw;
+  MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&mw, w_bf16, 0, 3), "conv2_fprop: tensor map encode failed");
+  static bool attr = false;
+  if (int e = set_smem(conv2_fprop_pool_kernel, fp::kSmem, &attr)) return e;
+  conv2_fprop_pool_kernel<<<grid_for(B), kThreads, fp::kSmem, stream>>>(mx, mw, bias, reinterpret_cast<bf16*>(out_bf16),
+                                                                       idx, B);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int B, cudaStream_t stream) {
+  MTB_REQUIRE(dy_bf16 && w_bf16 && dx_bf16 && B > 0, "conv2_dgrad: bad argument");
+  CUtensorMap md, mw;
+  MTB_REQUIRE(get_map(&md, dy_bf16, B, 1) && get_map(&mw, w_bf16, 0, 3), "conv2_dgrad: tensor map encode failed");
+  static bool attr = false;
+  if (int e = set_smem(conv2_dgrad_kernel, dg::kSmem, &attr)) return e;
+  conv2_dgrad_kernel<<<grid_for(B), kThreads, dg::kSmem, stream>>>(md, mw, reinterpret_cast<bf16*>(dx_bf16), B);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+size_t mtb_conv2_wgrad_workspace_bytes(int B) { return (size_t)grid_for(B) * wg::kPartialFloats * sizeof(float); }
+
+// dW is overwritten; db is accumulated into (the caller zeroes it once per step).
+int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* db, void* workspace, int B,
+                    cudaStream_t stream) {
+  MTB_REQUIRE(x_bf16 && dy_bf16 && dW && db && workspace && B > 0, "conv2_wgrad: bad argument");
+  CUtensorMap mx, md;
+  MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&md, dy_bf16, B, 2), "conv2_wgrad: tensor map encode failed");
+  static bool attr = false;
+  if (int e = set_smem(conv2_wgrad_kernel, wg::kSmem, &attr)) return e;
+  const int grid = grid_for(B);
+  conv2_wgrad_kernel<<<grid, kThreads, wg::kSmem, stream>>>(mx, md, reinterpret_cast<float*>(workspace), db, B);
+  MTB_LAUNCH_CHECK();
+  conv2_wgrad_reduce_kernel<<<(TAPS * CIN * COUT + 255) / 256, 256, 0, stream>>>(
+      reinterpret_cast<const float*>(workspace), dW, grid);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -74,6 +74,19 @@ int mtb_unpool_relu_bwd(const void* dP, const void* P, const uint8_t* idx, void*
 int mtb_im2col_5x5(const void* x, void* col, int B, int H, int W, int C, cudaStream_t stream);
 int mtb_col2im_5x5(const void* dcol, void* dx, int B, int H, int W, int C, cudaStream_t stream);
 
+/* ---- conv2 as implicit GEMM on tcgen05, no im2col (tf.nn.conv2d + relu + max_pool, mpipy.py:159-161, and the
+ *      Conv2DBackpropInput / Conv2DBackpropFilter ops TF autodiff adds for mpipy.py:65).  14x14 maps, 32 -> 64 ch. */
+int mtb_conv2_supported(int H, int cin, int cout);
+int mtb_conv2_fprop_pool(const void* x_bf16, const void* w_bf16, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                         cudaStream_t stream);
+int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int B, cudaStream_t stream);
+size_t mtb_conv2_wgrad_workspace_bytes(int B);
+int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* db, void* workspace, int B,
+                    cudaStream_t stream);
+/* probe of the shared-memory descriptor semantics the implicit-GEMM convolutions rely on (test only) */
+int mtb_debug_shift_mma(const void* A, const void* B, float* out, int mode, int row_bytes, int rows_total, int shift,
+                        int base_off, cudaStream_t stream);
+
 /* ---- FC2 + softmax + cross-entropy, forward and backward (mpipy.py:167, :55-56, :67-68) ---- */
 int mtb_fc2_softmax_ce(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
                        float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,

@@ -58,6 +58,7 @@ class TrainConfig:
     log_jsonl: Optional[str] = None
     log_all_ranks: bool = False
     # runtime
+    conv_impl: str = "auto"             # auto | implicit (shift-GEMM, no im2col) | im2col (+ GEMM)
     cuda_graph: bool = True
     checkpoint_dir: Optional[str] = None
     checkpoint_every: int = 0

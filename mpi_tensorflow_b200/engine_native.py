@@ -112,15 +112,23 @@ class NativeEngine:
         self.dh, self.dflat = z(Bmax, s.fc), z(Bmax, s.flat_dim)
         self.da2 = z(Bmax, 14, 14, s.c2)
         self.dp1 = z(Bmax, 14, 14, s.c1)
-        # generic (im2col) convolution path
-        self.col = z(Bmax * 196, 25 * s.c1)
-        self.a2 = z(Bmax * 196, s.c2)
-        self.dcol = z(Bmax * 196, 25 * s.c1)
-        # split-K scratch for the conv2 weight gradient (K = B*196 is the long axis)
-        self.wg_splits = 16
-        ws, cn = N.gemm_scratch_sizes(25 * s.c1, s.c2, 64, self.wg_splits)
-        self.wg_ws = torch.zeros(max(ws, 16), dtype=torch.uint8, device=dev)
-        self.wg_cnt = torch.zeros(max(cn, 16), dtype=torch.uint8, device=dev)
+        # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
+        want = self.conv_impl
+        have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2))
+        if want == "implicit" and not have:
+            raise ValueError(f"no implicit-GEMM conv2 kernel for {s.c1}->{s.c2} channels")
+        self.conv2_implicit = have and want != "im2col"
+        if self.conv2_implicit:
+            self.c2_ws = torch.zeros(N.lib().mtb_conv2_wgrad_workspace_bytes(Bmax), dtype=torch.uint8, device=dev)
+        else:
+            self.col = z(Bmax * 196, 25 * s.c1)
+            self.a2 = z(Bmax * 196, s.c2)
+            self.dcol = z(Bmax * 196, 25 * s.c1)
+            # split-K scratch for the conv2 weight gradient (K = B*196 is the long axis)
+            self.wg_splits = 16
+            ws, cn = N.gemm_scratch_sizes(25 * s.c1, s.c2, 64, self.wg_splits)
+            self.wg_ws = torch.zeros(max(ws, 16), dtype=torch.uint8, device=dev)
+            self.wg_cnt = torch.zeros(max(cn, 16), dtype=torch.uint8, device=dev)
 
     # ------------------------------------------------------------------ parameters
     def init_params(self, seed: int):
@@ -200,12 +208,17 @@ class NativeEngine:
         # conv1 + bias + ReLU + pool (mpipy.py:156-158)
         N.call("mtb_conv1_fwd", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
                self.a1p.data_ptr(), self.idx1.data_ptr(), B, s.c1)
-        # conv2 + bias + ReLU (mpipy.py:159-160) as im2col + tcgen05 GEMM, then pool (mpipy.py:161)
+        # conv2 + bias + ReLU + pool (mpipy.py:159-161)
         M2, K2 = B * 196, 25 * s.c1
-        N.call("mtb_im2col_5x5", self.a1p.data_ptr(), self.col.data_ptr(), B, 14, 14, s.c1)
-        N.gemm_bf16(self.col, S["conv2_weight"].view(K2, s.c2), self.a2, M2, s.c2, K2, False, True,
-                    bias=P["conv2_bias"], relu=True)
-        N.call("mtb_maxpool2x2_fwd", self.a2.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B, 14, 14, s.c2)
+        if self.conv2_implicit:
+            N.call("mtb_conv2_fprop_pool", self.a1p.data_ptr(), S["conv2_weight"].data_ptr(),
+                   P["conv2_bias"].data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B)
+        else:
+            N.call("mtb_im2col_5x5", self.a1p.data_ptr(), self.col.data_ptr(), B, 14, 14, s.c1)
+            N.gemm_bf16(self.col, S["conv2_weight"].view(K2, s.c2), self.a2, M2, s.c2, K2, False, True,
+                        bias=P["conv2_bias"], relu=True)
+            N.call("mtb_maxpool2x2_fwd", self.a2.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B, 14, 14,
+                   s.c2)
         # FC1 + bias + ReLU + dropout in the GEMM epilogue (mpipy.py:165-166)
         flat = self.a2p.view(self.Bmax, s.flat_dim)
         N.gemm_bf16(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
@@ -237,13 +250,19 @@ class NativeEngine:
         N.call("mtb_unpool_relu_bwd", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
                self.da2.data_ptr(), B, 14, 14, s.c2)
         da2 = self.da2.view(self.Bmax * 196, s.c2)
-        N.call("mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
-        # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
-        N.gemm_bf16(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
-                    splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
-        # conv2 dgrad: dcol = da2 W2^T, then col2im
-        N.gemm_bf16(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
-        N.call("mtb_col2im_5x5", self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
+        if self.conv2_implicit:
+            # wgrad (+ bias grad) and dgrad as shift-GEMMs straight from the activation / gradient maps
+            N.call("mtb_conv2_wgrad", self.a1p.data_ptr(), da2.data_ptr(), G["conv2_weight"].data_ptr(),
+                   G["conv2_bias"].data_ptr(), self.c2_ws.data_ptr(), B)
+            N.call("mtb_conv2_dgrad", da2.data_ptr(), S["conv2_weight"].data_ptr(), self.dp1.data_ptr(), B)
+        else:
+            N.call("mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
+            # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
+            N.gemm_bf16(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
+                        splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
+            # conv2 dgrad: dcol = da2 W2^T, then col2im
+            N.gemm_bf16(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
+            N.call("mtb_col2im_5x5", self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
         # pool1 + ReLU backward fused into the conv1 weight gradient
         N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
                self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)

@@ -65,6 +65,10 @@ _SIGS = {
     "mtb_fused_allreduce_update": [C.POINTER(FusedArgs), vp],
     "mtb_p2p_barrier": [C.POINTER(FusedArgs), vp],
     "mtb_advance_step": [vp, vp],
+    "mtb_debug_shift_mma": [vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "mtb_conv2_fprop_pool": [vp, vp, vp, vp, vp, i32, vp],
+    "mtb_conv2_dgrad": [vp, vp, vp, i32, vp],
+    "mtb_conv2_wgrad": [vp, vp, vp, vp, vp, i32, vp],
 }
 
 
@@ -90,6 +94,10 @@ def lib() -> C.CDLL:
     L.mtb_gemm_workspace_bytes.restype = C.c_size_t
     L.mtb_gemm_counter_bytes.argtypes = [i32, i32, i32]
     L.mtb_gemm_counter_bytes.restype = C.c_size_t
+    L.mtb_conv2_supported.argtypes = [i32, i32, i32]
+    L.mtb_conv2_supported.restype = i32
+    L.mtb_conv2_wgrad_workspace_bytes.argtypes = [i32]
+    L.mtb_conv2_wgrad_workspace_bytes.restype = C.c_size_t
     L.mtb_fused_max_blocks.restype = i32
     L.mtb_fused_flag_bytes.restype = i32
     _LIB = L

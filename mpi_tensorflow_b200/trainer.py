@@ -37,7 +37,7 @@ def make_engine(cfg: TrainConfig, comm: Communicator, device: torch.device):
     spec = get_spec(cfg.model)
     if device.type == "cuda":
         from .engine_native import NativeEngine
-        return NativeEngine(spec, cfg, comm, device)
+        return NativeEngine(spec, cfg, comm, device, conv_impl=cfg.conv_impl)
     from .engine_cpu import CpuEngine
     return CpuEngine(spec, cfg)
 

@@ -314,3 +314,71 @@ def test_fused_update_single_gpu_matches_oracle(N, dev, opt):
     assert torch.allclose(W.cpu(), ref, atol=2e-6, rtol=2e-5)
     assert torch.equal(S.cpu(), W.cpu().to(torch.bfloat16))
     assert int(status) == 0
+
+
+# ----------------------------------------------------------------------------- descriptor probe
+@pytest.mark.parametrize("mode,rb", [(0, 128), (0, 64), (1, 128)])
+def test_smem_descriptor_row_shift(N, dev, mode, rb):
+    """A tcgen05 operand may start at any row of a swizzled tile with base-offset 0: the
+    property the shift-GEMM convolutions are built on."""
+    rows = 256 if mode == 0 else 96
+    if mode == 0:
+        A = _bf(torch.randn(rows, rb // 2)).to(dev)
+        B = _bf(torch.randn(64, rb // 2)).to(dev)
+    else:
+        A = _bf(torch.randn(rows, 128)).to(dev)
+        B = _bf(torch.randn(64, 32)).to(dev)
+    for shift in (0, 1, 5, 18, 37, 64):
+        out = torch.zeros(128, 64, device=dev)
+        N.call("mtb_debug_shift_mma", A.data_ptr(), B.data_ptr(), out.data_ptr(), mode, rb, rows, shift, 0)
+        torch.cuda.synchronize()
+        ref = (A[shift:shift + 128].float() @ B.float().t()) if mode == 0 else \
+            (A[shift:shift + 32].float().t() @ B.float().t())
+        assert _rel(out, ref) < 1e-5
+
+
+# ----------------------------------------------------------------------------- conv2 implicit GEMM
+@pytest.mark.parametrize("B", [1, 3, 150, 301])
+def test_conv2_fprop_pool_implicit_gemm(N, dev, B):
+    x = _bf(torch.relu(torch.randn(B, 14, 14, 32))).to(dev)
+    w = _bf(torch.randn(5, 5, 32, 64) * 0.05).to(dev)
+    bias = (torch.randn(64) * 0.1).to(dev)
+    out = torch.zeros(B, 7, 7, 64, dtype=torch.bfloat16, device=dev)
+    idx = torch.full((B, 7, 7, 64), 9, dtype=torch.uint8, device=dev)
+    N.call("mtb_conv2_fprop_pool", x.data_ptr(), w.data_ptr(), bias.data_ptr(), out.data_ptr(), idx.data_ptr(), B)
+    torch.cuda.synchronize()
+    a = torch.relu(O.conv5x5(x.cpu().float(), w.cpu().float()) + bias.cpu())
+    a = a.to(torch.bfloat16).float()                      # the kernel pools the bf16-rounded activation
+    p, i = O.maxpool2x2(a)
+    got = out.cpu().float()
+    assert float((got - p).abs().max()) < 0.03 * max(1.0, float(p.abs().max()))
+    assert _rel(got, p) < 5e-3
+    assert ((idx.cpu().long() == i.long()).float().mean()) > 0.995
+    assert int(idx.max()) <= 3
+
+
+@pytest.mark.parametrize("B", [1, 5, 149, 300])
+def test_conv2_dgrad_implicit_gemm(N, dev, B):
+    dy = _bf(torch.randn(B, 14, 14, 64)).to(dev)
+    w = _bf(torch.randn(5, 5, 32, 64) * 0.05).to(dev)
+    dx = torch.zeros(B, 14, 14, 32, dtype=torch.bfloat16, device=dev)
+    N.call("mtb_conv2_dgrad", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), B)
+    torch.cuda.synchronize()
+    ref = O.conv5x5_dgrad(dy.cpu().float(), w.cpu().float(), (B, 14, 14, 32))
+    assert _rel(dx.cpu(), ref) < 5e-3
+
+
+@pytest.mark.parametrize("B", [1, 4, 148, 333])
+def test_conv2_wgrad_implicit_gemm(N, dev, B):
+    x = _bf(torch.relu(torch.randn(B, 14, 14, 32))).to(dev)
+    dy = _bf(torch.randn(B, 14, 14, 64) * (torch.rand(B, 14, 14, 64) < 0.25)).to(dev)
+    dW = torch.full((800, 64), float("nan"), device=dev)
+    db = torch.zeros(64, device=dev)
+    ws = torch.zeros(N.lib().mtb_conv2_wgrad_workspace_bytes(B), dtype=torch.uint8, device=dev)
+    for rep in range(2):
+        db.zero_()
+        N.call("mtb_conv2_wgrad", x.data_ptr(), dy.data_ptr(), dW.data_ptr(), db.data_ptr(), ws.data_ptr(), B)
+        torch.cuda.synchronize()
+        ref = O.conv5x5_wgrad(x.cpu().float(), dy.cpu().float()).reshape(800, 64)
+        assert _rel(dW.cpu(), ref) < 1e-4
+        assert _rel(db.cpu(), dy.cpu().float().sum((0, 1, 2))) < 1e-4
