@@ -47,6 +47,7 @@ constexpr int PATCH_ROWS = PWID * PWID;  // 324
 constexpr int W_BYTES = TAPS * CIN * COUT * 2;      // 102400: every tap's [32 ci][64 co] tile
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar256() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // ======================================================================================= fprop
 namespace fp {
@@ -56,10 +57,11 @@ constexpr int kOffW = 0;
 constexpr int kOffPatch = W_BYTES;
 constexpr int kOffStage = kOffPatch + kStages * kPatchBytes;   // bf16 [256][64] relu'd tile for pooling
 constexpr int kOffBar = kOffStage + 256 * 128;
-constexpr int kSmem = 1024 + kOffBar + 128;
+constexpr int kSmem = 1024 + kOffBar + 128 + 256;
+constexpr int kThreadsFp = 64 + 256;                       // TMA warp, MMA warp, 8 epilogue warps
 }  // namespace fp
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(fp::kThreadsFp, 1)
 conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                         const float* __restrict__ bias, bf16* __restrict__ out, uint8_t* __restrict__ idx, int B) {
   using namespace fp;
@@ -74,14 +76,16 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   uint64_t* a_full = p_empty + kStages;
   uint64_t* a_empty = a_full + 2;
   uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
+  float* sBias = reinterpret_cast<float*>(smem + kOffBar + 128);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+  if (threadIdx.x < COUT) sBias[threadIdx.x] = __ldg(bias + threadIdx.x);
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_w);
     mbar_init(w_full, 1);
     for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], 1); mbar_init(&p_empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 8); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<256>(holder);
@@ -104,7 +108,7 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, COUT, false, true);
       mbar_wait(w_full, 0);
       int it = 0;
@@ -114,20 +118,23 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         mbar_wait(&p_full[s], ph);
         mbar_wait(&a_empty[a], aph ^ 1);
         tc_fence_after();
-        const uint32_t pbase = smem_u32(sPatch + s * kPatchBytes);
-        const uint32_t wbase = smem_u32(sW);
-#pragma unroll 1
+        // descriptors differ only in their 14-bit start-address field: build one per operand,
+        // then every MMA is a 64-bit add with a compile-time offset (the single issuing thread
+        // is the critical path of this kernel)
+        const uint64_t a0 = make_smem_desc(smem_u32(sPatch + s * kPatchBytes), 16, 512, kSwizzle64B);
+        const uint64_t b0 = make_smem_desc(smem_u32(sW), 4096, 1024, kSwizzle128B);
+#pragma unroll
         for (int tile = 0; tile < 2; ++tile) {
           const uint32_t d = tmem + a * 128 + tile * 64;
-#pragma unroll 1
+#pragma unroll
           for (int tap = 0; tap < TAPS; ++tap) {
             const int shift = (tap / 5) * PWID + (tap % 5);
-            const uint32_t arow = pbase + (uint32_t)(tile * 128 + shift) * 64;
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
-              const uint64_t da = make_smem_desc(arow + k * 32, 16, 512, kSwizzle64B);
-              const uint64_t db = make_smem_desc(wbase + tap * 4096 + k * 2048, 4096, 1024, kSwizzle128B);
-              mma_f16(d, da, db, idesc, (tap | k) != 0);
+              const uint64_t da = a0 + (uint64_t)(((tile * 128 + shift) * 64 + k * 32) >> 4);
+              const uint64_t db = b0 + (uint64_t)((tap * 4096 + k * 2048) >> 4);
+              if (tap == 0 && k == 0) mma_f16_first(d, da, db, idesc);
+              else mma_f16_acc(d, da, db, idesc);
             }
           }
         }
@@ -137,32 +144,40 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
     }
     __syncwarp();
   } else {
+    // 8 warps: warp%4 picks the TMEM lane quadrant, (warp-2)/4 picks which of the two M tiles
     const int q = warp & 3;
+    const int tile = (warp - 2) >> 2;
     const int t128 = q * 32 + lane;                 // 0..127: TMEM lane = row within a tile
+    const int t256 = tile * 128 + t128;
     int it = 0;
     for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
       const int a = it & 1, aph = (it >> 1) & 1;
       mbar_wait(&a_full[a], aph);
       tc_fence_after();
-#pragma unroll 1
-      for (int tile = 0; tile < 2; ++tile) {
+      {
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + a * 128 + tile * 64;
-        const int row = tile * 128 + t128;
+        const int row = t256;
         uint8_t* dst = sStage + row * 128;
-#pragma unroll 1
+        uint32_t r0[32], r1[32];
+        tmem_ld_32x32(taddr, r0);
+        tmem_ld_32x32(taddr + 32, r1);
+        tmem_ld_wait();
+#pragma unroll
         for (int c = 0; c < 2; ++c) {
-          uint32_t r[32];
-          tmem_ld_32x32(taddr + c * 32, r);
-          tmem_ld_wait();
+          const uint32_t* r = c == 0 ? r0 : r1;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            float v[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-              v[e] = fmaxf(__uint_as_float(r[8 * j + e]) + __ldg(bias + c * 32 + 8 * j + e), 0.f);
+            const float4 b0 = *reinterpret_cast<const float4*>(sBias + c * 32 + 8 * j);
+            const float4 b1 = *reinterpret_cast<const float4*>(sBias + c * 32 + 8 * j + 4);
             uint4 pk;
-            pk.x = mtb::pack_bf16x2(v[0], v[1]); pk.y = mtb::pack_bf16x2(v[2], v[3]);
-            pk.z = mtb::pack_bf16x2(v[4], v[5]); pk.w = mtb::pack_bf16x2(v[6], v[7]);
+            pk.x = mtb::pack_bf16x2(fmaxf(__uint_as_float(r[8 * j + 0]) + b0.x, 0.f),
+                                    fmaxf(__uint_as_float(r[8 * j + 1]) + b0.y, 0.f));
+            pk.y = mtb::pack_bf16x2(fmaxf(__uint_as_float(r[8 * j + 2]) + b0.z, 0.f),
+                                    fmaxf(__uint_as_float(r[8 * j + 3]) + b0.w, 0.f));
+            pk.z = mtb::pack_bf16x2(fmaxf(__uint_as_float(r[8 * j + 4]) + b1.x, 0.f),
+                                    fmaxf(__uint_as_float(r[8 * j + 5]) + b1.y, 0.f));
+            pk.w = mtb::pack_bf16x2(fmaxf(__uint_as_float(r[8 * j + 6]) + b1.z, 0.f),
+                                    fmaxf(__uint_as_float(r[8 * j + 7]) + b1.w, 0.f));
             const int chunk = c * 4 + j;
             *reinterpret_cast<uint4*>(dst + ((chunk ^ (row & 7)) << 4)) = pk;
           }
@@ -171,9 +186,9 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&a_empty[a]);
-      epi_bar();                                     // staging tile complete
+      epi_bar256();                                  // staging tile complete
       // 2x2 max-pool + argmax (first max wins, order (0,0),(0,1),(1,0),(1,1))
-      for (int item = t128; item < 49 * 8; item += 128) {
+      for (int item = t256; item < 49 * 8; item += 256) {
         const int pp = item >> 3, chunk = item & 7;
         const int ph = pp / 7, pw = pp % 7;
         const int m00 = (2 * ph) * PWID + 2 * pw;
@@ -201,7 +216,7 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         k2.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
         *reinterpret_cast<uint2*>(idx + off) = k2;
       }
-      epi_bar();                                     // staging tile free for the next image
+      epi_bar256();                                  // staging tile free for the next image
     }
     tc_fence_before();
   }
@@ -263,7 +278,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, CIN, false, false);
       mbar_wait(w_full, 0);
       int it = 0;
@@ -273,21 +288,20 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
         mbar_wait(&p_full[s], ph);
         mbar_wait(&a_empty[a], aph ^ 1);
         tc_fence_after();
-        const uint32_t pbase = smem_u32(sPatch + s * kPatchBytes);
-        const uint32_t wbase = smem_u32(sW);
-#pragma unroll 1
+        const uint64_t a0 = make_smem_desc(smem_u32(sPatch + s * kPatchBytes), 16, 1024, kSwizzle128B);
+        const uint64_t b0 = make_smem_desc(smem_u32(sW), 16, 1024, kSwizzle128B);
+#pragma unroll
         for (int tile = 0; tile < 2; ++tile) {
           const uint32_t d = tmem + a * 64 + tile * 32;
-#pragma unroll 1
+#pragma unroll
           for (int tap = 0; tap < TAPS; ++tap) {      // tap' = flipped tap: weight slot 24 - tap'
             const int shift = (tap / 5) * PWID + (tap % 5);
-            const uint32_t arow = pbase + (uint32_t)(tile * 128 + shift) * 128;
-            const uint32_t wrow = wbase + (uint32_t)(TAPS - 1 - tap) * 4096;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const uint64_t da = make_smem_desc(arow + k * 32, 16, 1024, kSwizzle128B);
-              const uint64_t db = make_smem_desc(wrow + k * 32, 16, 1024, kSwizzle128B);
-              mma_f16(d, da, db, idesc, (tap | k) != 0);
+              const uint64_t da = a0 + (uint64_t)(((tile * 128 + shift) * 128 + k * 32) >> 4);
+              const uint64_t db = b0 + (uint64_t)(((TAPS - 1 - tap) * 4096 + k * 32) >> 4);
+              if (tap == 0 && k == 0) mma_f16_first(d, da, db, idesc);
+              else mma_f16_acc(d, da, db, idesc);
             }
           }
         }
@@ -349,8 +363,9 @@ constexpr int kOffBar = kStages * kStageBytes;
 constexpr int kOffRed = kOffBar + 128;                     // fp32 [16][64] bias partials
 constexpr int kSmem = 1024 + kOffRed + 16 * 64 * 4;
 constexpr int kKSteps = 18;                                // 288 pixel rows / 16
-constexpr int kCols = 480;                                 // 3 MMAs x N=160
+constexpr int kCols = 160;                                 // one N=160 MMA per CTA (see the group split below)
 constexpr int kPartialFloats = kCols * 128;
+constexpr int kMaxPerGroup = 49;                           // 3 groups x 49 CTAs = 147 SMs
 }  // namespace wg
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -378,17 +393,22 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     mbar_init(a_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<512>(holder);
+  if (warp == 1) tmem_alloc<256>(holder);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
-  const int n_img = blockIdx.x < B ? (B - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+  // CTA group j = blockIdx % 3 owns filter rows kh_j (TMEM lanes 64..127) and kh_j + 2 (lanes 0..63),
+  // kh_j = 0, 1, 4, over a third of the CTAs each: three times fewer per-CTA partial sums to
+  // write and reduce than letting every CTA hold all 25 taps.
+  const int grp = blockIdx.x % 3, g_idx = blockIdx.x / 3, g_cnt = gridDim.x / 3;
+  const int kh_j = grp == 2 ? 4 : grp;
+  const int n_img = g_idx < B ? (B - 1 - g_idx) / g_cnt + 1 : 0;
 
   if (warp == 0) {
     if (lane == 0) {
       int it = 0;
-      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      for (int img = g_idx; img < B; img += g_cnt, ++it) {
         const int s = it % kStages, ph = (it / kStages) & 1;
         mbar_wait(&p_empty[s], ph ^ 1);
         uint8_t* st = smem + s * kStageBytes;
@@ -399,25 +419,23 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, 160, true, true);
       int it = 0;
-      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      for (int img = g_idx; img < B; img += g_cnt, ++it) {
         const int s = it % kStages, ph = (it / kStages) & 1;
         mbar_wait(&p_full[s], ph);
         tc_fence_after();
-        const uint32_t dy0 = smem_u32(smem + s * kStageBytes) + (kLead - 36) * 128;   // row p-36 of dy
-        const uint32_t x0 = smem_u32(smem + s * kStageBytes + kDyBytes);
-#pragma unroll 1
-        for (int ks = 0; ks < kKSteps; ++ks) {
-          const uint64_t da = make_smem_desc(dy0 + ks * 2048, 36 * 128, 1024, kSwizzle128B);
+        // A starts at row p-36 of dy; B at row p + 18 kh of the x patch
+        const uint64_t a0 = make_smem_desc(smem_u32(smem + s * kStageBytes) + (kLead - 36) * 128, 36 * 128, 1024,
+                                           kSwizzle128B);
+        const uint64_t b0 = make_smem_desc(smem_u32(smem + s * kStageBytes + kDyBytes) + kh_j * PWID * 64, 64, 512,
+                                           kSwizzle64B);
+        if (it == 0) mma_f16_first(tmem, a0, b0, idesc);
+        else mma_f16_acc(tmem, a0, b0, idesc);
 #pragma unroll
-          for (int j = 0; j < 3; ++j) {
-            const int kh = j == 2 ? 4 : j;
-            const uint64_t db_ = make_smem_desc(x0 + (uint32_t)(ks * 16 + kh * PWID) * 64, 64, 512, kSwizzle64B);
-            mma_f16(tmem + j * 160, da, db_, idesc, (it | ks) != 0);
-          }
-        }
+        for (int ks = 1; ks < kKSteps; ++ks)
+          mma_f16_acc(tmem, a0 + (uint64_t)((ks * 2048) >> 4), b0 + (uint64_t)((ks * 16 * 64) >> 4), idesc);
         mma_commit(&p_empty[s]);
       }
       mma_commit(a_full);
@@ -432,11 +450,11 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
     int it = 0;
-    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+    for (int img = g_idx; img < B; img += g_cnt, ++it) {
       const int s = it % kStages, ph = (it / kStages) & 1;
       mbar_wait(&p_full[s], ph);
       const uint8_t* dy = smem + s * kStageBytes + kLead * 128;
-      for (int r = sub; r < M_ROWS; r += 16) {
+      for (int r = sub; grp == 0 && r < M_ROWS; r += 16) {
         const uint4 pk = *reinterpret_cast<const uint4*>(dy + r * 128 + ((chunk ^ (r & 7)) << 4));
         const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
 #pragma unroll
@@ -452,7 +470,7 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 #pragma unroll
     for (int e = 0; e < 8; ++e) sRed[sub * 64 + chunk * 8 + e] = acc[e];
     epi_bar();
-    if (t128 < 64 && n_img > 0) {
+    if (t128 < 64 && n_img > 0 && grp == 0) {
       float s = 0.f;
 #pragma unroll
       for (int i = 0; i < 16; ++i) s += sRed[i * 64 + t128];
@@ -475,11 +493,11 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     }
   }
   __syncthreads();
-  if (warp == 1) { tc_fence_after(); tmem_dealloc<512>(tmem); }
+  if (warp == 1) { tc_fence_after(); tmem_dealloc<256>(tmem); }
 }
 
-// dW[(kh*5+kw)*32+ci][co] = sum over CTAs of partial[cta][j*160 + kw*32 + ci][lane]
-//   kh 0,1,4 -> j 0,1,2, lane 64+co   |   kh 2,3 -> j 0,1, lane co
+// dW[(kh*5+kw)*32+ci][co] = sum over the CTAs c of group j of partial[c][kw*32 + ci][lane], in CTA order
+//   kh 0,1,4 -> group 0,1,2, lane 64+co   |   kh 2,3 -> group 0,1, lane co
 __global__ void __launch_bounds__(256)
 conv2_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dW, int n_cta) {
   const int o = blockIdx.x * blockDim.x + threadIdx.x;
@@ -489,16 +507,18 @@ conv2_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__
   int j, lane;
   if (kh == 2 || kh == 3) { j = kh - 2; lane = co; }
   else { j = kh == 4 ? 2 : kh; lane = 64 + co; }
-  const float* src = partial + (size_t)(j * 160 + kw * 32 + ci) * 128 + lane;
+  const float* src = partial + (size_t)j * wg::kPartialFloats + (size_t)(kw * 32 + ci) * 128 + lane;
+  const size_t stride = (size_t)3 * wg::kPartialFloats;
+  const int n = n_cta / 3;
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   int c = 0;
-  for (; c + 4 <= n_cta; c += 4) {
-    s0 += __ldcs(src + (size_t)(c + 0) * wg::kPartialFloats);
-    s1 += __ldcs(src + (size_t)(c + 1) * wg::kPartialFloats);
-    s2 += __ldcs(src + (size_t)(c + 2) * wg::kPartialFloats);
-    s3 += __ldcs(src + (size_t)(c + 3) * wg::kPartialFloats);
+  for (; c + 4 <= n; c += 4) {
+    s0 += __ldcs(src + (size_t)(c + 0) * stride);
+    s1 += __ldcs(src + (size_t)(c + 1) * stride);
+    s2 += __ldcs(src + (size_t)(c + 2) * stride);
+    s3 += __ldcs(src + (size_t)(c + 3) * stride);
   }
-  for (; c < n_cta; ++c) s0 += __ldcs(src + (size_t)c * wg::kPartialFloats);
+  for (; c < n; ++c) s0 += __ldcs(src + (size_t)c * stride);
   dW[o] = (s0 + s1) + (s2 + s3);
 }
 
@@ -563,7 +583,7 @@ int mtb_conv2_fprop_pool(const void* x_bf16, const void* w_bf16, const float* bi
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&mw, w_bf16, 0, 3), "conv2_fprop: tensor map encode failed");
   static bool attr = false;
   if (int e = set_smem(conv2_fprop_pool_kernel, fp::kSmem, &attr)) return e;
-  conv2_fprop_pool_kernel<<<grid_for(B), kThreads, fp::kSmem, stream>>>(mx, mw, bias, reinterpret_cast<bf16*>(out_bf16),
+  conv2_fprop_pool_kernel<<<grid_for(B), fp::kThreadsFp, fp::kSmem, stream>>>(mx, mw, bias, reinterpret_cast<bf16*>(out_bf16),
                                                                        idx, B);
   MTB_LAUNCH_CHECK();
   return 0;
@@ -580,7 +600,8 @@ int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int 
   return 0;
 }
 
-size_t mtb_conv2_wgrad_workspace_bytes(int B) { return (size_t)grid_for(B) * wg::kPartialFloats * sizeof(float); }
+static int wgrad_grid(int B) { return 3 * (B < wg::kMaxPerGroup ? B : wg::kMaxPerGroup); }
+size_t mtb_conv2_wgrad_workspace_bytes(int B) { return (size_t)wgrad_grid(B) * wg::kPartialFloats * sizeof(float); }
 
 // dW is overwritten; db is accumulated into (the caller zeroes it once per step).
 int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* db, void* workspace, int B,
@@ -590,7 +611,7 @@ int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* d
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&md, dy_bf16, B, 2), "conv2_wgrad: tensor map encode failed");
   static bool attr = false;
   if (int e = set_smem(conv2_wgrad_kernel, wg::kSmem, &attr)) return e;
-  const int grid = grid_for(B);
+  const int grid = wgrad_grid(B);
   conv2_wgrad_kernel<<<grid, kThreads, wg::kSmem, stream>>>(mx, md, reinterpret_cast<float*>(workspace), db, B);
   MTB_LAUNCH_CHECK();
   conv2_wgrad_reduce_kernel<<<(TAPS * CIN * COUT + 255) / 256, 256, 0, stream>>>(

@@ -92,7 +92,82 @@ shift_probe_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_const
   if (warp == 0) { tc_fence_after(); tmem_dealloc<64>(tmem); }
 }
 
+// Hand-written (no TMA) 32-byte-row tiles, the layout the first convolution layer builds in
+// shared memory itself:
+//   mode 2: A K-major SW32 [rows][16 bf16], tile = rows [shift, shift+128); B K-major SW32 [32][16]
+//   mode 3: A MN-major SW32: K = 16 rows [shift, shift+16), M = 8 atoms of 16, atom a = the same
+//           tile moved down by a*atom_rows rows (LBO = atom_rows*32 bytes); B MN-major SW64 [16][32]
+__global__ void __launch_bounds__(128, 1)
+shift_probe32_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __restrict__ B, float* __restrict__ out,
+                     int mode, int rows_total, int shift, int atom_rows) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                       // rows_total * 32 B
+  uint8_t* sB = smem + 16384;
+  uint64_t* done = reinterpret_cast<uint64_t*>(smem + 16384 + 2048);
+  uint32_t* holder = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < rows_total * 2; i += blockDim.x) {
+    const int r = i >> 1, c = i & 1;
+    *reinterpret_cast<uint4*>(sA + r * 32 + ((c ^ ((r >> 2) & 1)) << 4)) =
+        *reinterpret_cast<const uint4*>(A + r * 16 + c * 8);
+  }
+  if (mode == 2) {
+    for (int i = threadIdx.x; i < 32 * 2; i += blockDim.x) {
+      const int r = i >> 1, c = i & 1;
+      *reinterpret_cast<uint4*>(sB + r * 32 + ((c ^ ((r >> 2) & 1)) << 4)) =
+          *reinterpret_cast<const uint4*>(B + r * 16 + c * 8);
+    }
+  } else {
+    for (int i = threadIdx.x; i < 16 * 4; i += blockDim.x) {
+      const int r = i >> 2, c = i & 3;
+      *reinterpret_cast<uint4*>(sB + r * 64 + ((c ^ ((r >> 1) & 3)) << 4)) =
+          *reinterpret_cast<const uint4*>(B + r * 32 + c * 8);
+    }
+  }
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) { mbar_init(done, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc<32>(holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+  if (warp == 1 && elect_one()) {
+    if (mode == 2) {
+      const uint32_t idesc = make_idesc(kFmtBF16, 128, 32, false, false);
+      mma_f16_first(tmem, make_smem_desc(smem_u32(sA) + shift * 32, 16, 256, kSwizzle32B),
+                    make_smem_desc(smem_u32(sB), 16, 256, kSwizzle32B), idesc);
+    } else {
+      const uint32_t idesc = make_idesc(kFmtBF16, 128, 32, true, true);
+      mma_f16_first(tmem, make_smem_desc(smem_u32(sA) + shift * 32, atom_rows * 32, 256, kSwizzle32B),
+                    make_smem_desc(smem_u32(sB), 64, 512, kSwizzle64B), idesc);
+    }
+    mma_commit(done);
+  }
+  __syncwarp();
+  mbar_wait(done, 0);
+  tc_fence_after();
+  uint32_t r[32];
+  tmem_ld_32x32(tmem + ((uint32_t)(warp * 32) << 16), r);
+  tmem_ld_wait();
+  for (int j = 0; j < 32; ++j) out[(warp * 32 + lane) * 32 + j] = __uint_as_float(r[j]);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { tc_fence_after(); tmem_dealloc<32>(tmem); }
+}
+
 }  // namespace
+
+extern "C" int mtb_debug_shift_mma32(const void* A, const void* B, float* out, int mode, int rows_total, int shift,
+                                     int atom_rows, cudaStream_t stream) {
+  MTB_REQUIRE(mode == 2 || mode == 3, "shift probe32: mode 2 or 3");
+  MTB_REQUIRE(rows_total <= 512, "shift probe32: at most 512 rows");
+  shift_probe32_kernel<<<1, 128, 1024 + 16384 + 2048 + 64, stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(A), reinterpret_cast<const __nv_bfloat16*>(B), out, mode, rows_total, shift,
+      atom_rows);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int mtb_debug_shift_mma(const void* A, const void* B, float* out, int mode, int row_bytes, int rows_total,
                                    int shift, int base_off, cudaStream_t stream) {

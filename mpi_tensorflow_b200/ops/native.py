@@ -66,6 +66,7 @@ _SIGS = {
     "mtb_p2p_barrier": [C.POINTER(FusedArgs), vp],
     "mtb_advance_step": [vp, vp],
     "mtb_debug_shift_mma": [vp, vp, vp, i32, i32, i32, i32, i32, vp],
+    "mtb_debug_shift_mma32": [vp, vp, vp, i32, i32, i32, i32, vp],
     "mtb_conv2_fprop_pool": [vp, vp, vp, vp, vp, i32, vp],
     "mtb_conv2_dgrad": [vp, vp, vp, i32, vp],
     "mtb_conv2_wgrad": [vp, vp, vp, vp, vp, i32, vp],
