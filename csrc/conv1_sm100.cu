@@ -1,0 +1,426 @@
+// First convolution layer (5x5, SAME, 1 -> 32 channels on 28x28 images; mpipy.py:156-158 and its
+// Conv2DBackpropFilter / ReluGrad / MaxPoolGrad ops) on tcgen05.
+//
+// One input channel means the implicit GEMM has K = 25, far too thin for TMA tiles (a pixel is
+// 2 bytes).  Instead each image is expanded 5x, not 25x, by CUDA cores into a shared-memory
+// operand "X5": one 32-byte row per pixel holding the pixel's five vertical neighbours
+//     X5[row(h,w)][kh] = x_pad[h+kh][w],  kh = 0..4;   X5[..][5] = 1;   X5[..][6..15] = 0
+// so the vertical taps are the K dimension (K = 16 = one bf16 MMA) and the horizontal tap kw is
+// a start-address shift of the same operand, as in conv2_sm100.cu.  Rows are ordered
+//     row = 128*(h/4) + 4*w + (h%4)          (w = 0..31, columns 28..31 are padding)
+// so (a) tap kw is a shift of 4*kw rows and (b) the four pixels of a 2x2 pooling window sit in
+// lanes L, L^1, L^4, L^5 of one warp: bias + ReLU + max-pool + argmax happen in registers with
+// 24 shuffles per 32 channels, and only the pooled bf16 map and the 2-bit argmax leave the SM.
+//
+//   fwd    D[pixel, c] = sum_kw X5[pixel + 4kw][0..15] . Wk[kw][c][0..15]      35 MMAs (128x32x16) per image
+//   wgrad  D[(kw,kh), c] = sum_pixel X5[pixel + 4kw][kh] . dA[pixel][c]        56 MMAs per image; both operands
+//          MN-major; the 8 M-atoms of the A operand are X5 moved down 4 rows each (kw = 0..7, 5 used).
+//          dA = pooled gradient routed to the argmax and gated by ReLU, rebuilt in shared memory
+//          from the pooled maps (never materialised in global memory).  The ones column of X5 makes
+//          lane (kw=0, kh=5) the bias gradient.
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace {
+
+using namespace sm100;
+using bf16 = __nv_bfloat16;
+
+constexpr int IMG = 28, C1 = 32;
+constexpr int X5_ROWS = 928;                 // 896 + 32: kw shifts (<= 28 rows) of the last tile stay in bounds
+constexpr int X5_BYTES = X5_ROWS * 32;       // 29696
+constexpr int XS_PITCH = 33;
+constexpr int XS_FLOATS = 32 * XS_PITCH;     // padded 32x32 image, pitch 33
+
+__device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+// padded image -> shared floats; xs[i][j] = x[i-2][j-2] (zero outside).  NT threads, all loads issued first.
+template <int NT>
+__device__ __forceinline__ void load_xs(float* xs, const float* __restrict__ x, int t) {
+  constexpr int PER = 1024 / NT;
+  float v[PER];
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    const int i = t + k * NT;
+    const int r = (i >> 5) - 2, c = (i & 31) - 2;
+    v[k] = (r >= 0 && r < IMG && c >= 0 && c < IMG) ? __ldg(x + r * IMG + c) : 0.f;
+  }
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    const int i = t + k * NT;
+    xs[(i >> 5) * XS_PITCH + (i & 31)] = v[k];
+  }
+}
+
+// X5 rows [0, 896) from the padded image.  Row R = 128t + 4w + hl  <->  pixel (h = 4t + hl, w).
+__device__ __forceinline__ void build_x5(uint8_t* x5, const float* xs, int t, int nthreads) {
+  for (int R = t; R < 896; R += nthreads) {
+    const int tile = R >> 7, w = (R >> 2) & 31, hl = R & 3;
+    const int h = tile * 4 + hl;
+    const float* p = xs + h * XS_PITCH + w;
+    uint4 v;
+    v.x = mtb::pack_bf16x2(p[0], p[XS_PITCH]);
+    v.y = mtb::pack_bf16x2(p[2 * XS_PITCH], p[3 * XS_PITCH]);
+    v.z = mtb::pack_bf16x2(p[4 * XS_PITCH], 1.0f);
+    v.w = 0u;
+    const int sw = w & 1;                                   // SW32: chunk ^= bit 7 of the byte address = (R>>2)&1
+    *reinterpret_cast<uint4*>(x5 + R * 32 + (sw << 4)) = v;
+    *reinterpret_cast<uint4*>(x5 + R * 32 + ((sw ^ 1) << 4)) = make_uint4(0, 0, 0, 0);
+  }
+}
+
+// ======================================================================================= forward
+namespace f1 {
+constexpr int kProducers = 128, kEpilogue = 256;            // kProducers per stage; one producer group per stage
+constexpr int kThreads = 32 + 2 * kProducers + kEpilogue;    // warp 0 MMA, 1-8 producers, 9-16 epilogue
+constexpr int kOffX5 = 0;                                    // 2 stages
+constexpr int kOffW = 2 * X5_BYTES;                          // 5 x [32 c][16 kh] SW32 = 5 KB
+constexpr int kOffXs = kOffW + 5 * 1024;                     // 2 x padded image
+constexpr int kOffBar = kOffXs + 2 * XS_FLOATS * 4;
+constexpr int kSmem = 1024 + kOffBar + 128;
+}  // namespace f1
+
+__global__ void __launch_bounds__(f1::kThreads, 1)
+conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25][32]*/, const float* __restrict__ bias,
+                    bf16* __restrict__ out, uint8_t* __restrict__ idx, int B) {
+  using namespace f1;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sX5 = smem + kOffX5;
+  uint8_t* sW = smem + kOffW;
+  float* sXs = reinterpret_cast<float*>(smem + kOffXs);
+  uint64_t* x_full = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* x_empty = x_full + 2;
+  uint64_t* a_full = x_empty + 2;
+  uint64_t* a_empty = a_full + 2;
+  uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // zero both X5 stages (tail rows and padding stay zero for the kernel's lifetime), build weights
+  for (int i = threadIdx.x; i < 2 * X5_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(sX5)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 5 * C1; i += kThreads) {
+    const int kw = i / C1, c = i % C1;
+    uint4 v;
+    v.x = mtb::pack_bf16x2(__ldg(w + (0 * 5 + kw) * C1 + c), __ldg(w + (1 * 5 + kw) * C1 + c));
+    v.y = mtb::pack_bf16x2(__ldg(w + (2 * 5 + kw) * C1 + c), __ldg(w + (3 * 5 + kw) * C1 + c));
+    v.z = mtb::pack_bf16x2(__ldg(w + (4 * 5 + kw) * C1 + c), 0.f);
+    v.w = 0u;
+    const int sw = (c >> 2) & 1;
+    *reinterpret_cast<uint4*>(sW + kw * 1024 + c * 32 + (sw << 4)) = v;
+    *reinterpret_cast<uint4*>(sW + kw * 1024 + c * 32 + ((sw ^ 1) << 4)) = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&x_full[s], kProducers);
+      mbar_init(&x_empty[s], 1);
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], kEpilogue / 32);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<512>(holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, C1, false, false);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it & 1, ph = (it >> 1) & 1;
+        mbar_wait(&x_full[s], ph);
+        mbar_wait(&a_empty[s], ph ^ 1);
+        tc_fence_after();
+        const uint64_t a0 = make_smem_desc(smem_u32(sX5 + s * X5_BYTES), 16, 256, kSwizzle32B);
+        const uint64_t b0 = make_smem_desc(smem_u32(sW), 16, 256, kSwizzle32B);
+#pragma unroll
+        for (int tile = 0; tile < 7; ++tile) {
+#pragma unroll
+          for (int kw = 0; kw < 5; ++kw) {
+            const uint64_t da = a0 + (uint64_t)(((tile * 128 + 4 * kw) * 32) >> 4);
+            const uint64_t db = b0 + (uint64_t)((kw * 1024) >> 4);
+            if (kw == 0) mma_f16_first(tmem + s * 256 + tile * 32, da, db, idesc);
+            else mma_f16_acc(tmem + s * 256 + tile * 32, da, db, idesc);
+          }
+        }
+        mma_commit(&x_empty[s]);
+        mma_commit(&a_full[s]);
+      }
+    }
+    __syncwarp();
+  } else if (warp <= 8) {
+    // producer group g owns stage g and every second image of this CTA, so two images are in flight
+    const int g = (warp - 1) >> 2;
+    const int t = threadIdx.x - 32 - g * kProducers;
+    float* xs = sXs + g * XS_FLOATS;
+    int it = g;
+    for (int img = blockIdx.x + g * gridDim.x; img < B; img += 2 * gridDim.x, it += 2) {
+      const int ph = (it >> 1) & 1;
+      mbar_wait(&x_empty[g], ph ^ 1);                        // MMAs that read this X5 stage have retired
+      load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);
+      named_bar(2 + g, kProducers);                          // padded image complete
+      build_x5(sX5 + g * X5_BYTES, xs, t, kProducers);
+      fence_proxy_async_smem();
+      mbar_arrive(&x_full[g]);
+      named_bar(2 + g, kProducers);                          // everyone is done reading xs
+    }
+  } else {
+    const int q = warp & 3;
+    const int half = (warp - 9) >> 2;                        // tiles with tile % 2 == half
+    const int L = q * 32 + lane;                             // TMEM lane = row within a tile
+    const int wcol = L >> 2, hl = L & 3;
+    const int dy = hl & 1, dx = wcol & 1;
+    const uint32_t pos_key = 3u - (uint32_t)(2 * dy + dx);
+    float bs[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) bs[j] = __ldg(bias + j);
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int s = it & 1, ph = (it >> 1) & 1;
+      mbar_wait(&a_full[s], ph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int tile = half; tile < 7; tile += 2) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + s * 256 + tile * 32, r);
+        tmem_ld_wait();
+        // key = relu(acc + bias) with the two low mantissa bits replaced by (3 - window position):
+        // an unsigned max picks the largest value and, on ties, the first position
+        uint32_t key[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float v = fmaxf(__uint_as_float(r[j]) + bs[j], 0.f);
+          key[j] = (__float_as_uint(v) & 0x7ffffffcu) | pos_key;          // also drops the sign of a -0.0
+        }
+        uint32_t m[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const uint32_t send = dy ? key[j] : key[16 + j];
+          const uint32_t keep = dy ? key[16 + j] : key[j];
+          m[j] = max(keep, __shfl_xor_sync(0xffffffffu, send, 1));
+        }
+        uint32_t f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t send = dx ? m[j] : m[8 + j];
+          const uint32_t keep = dx ? m[8 + j] : m[j];
+          f[j] = max(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+        }
+        if (wcol < IMG) {
+          const int h = tile * 4 + hl;
+          const int cbase = dy * 16 + dx * 8;
+          const size_t o = (((size_t)img * 14 + (h >> 1)) * 14 + (wcol >> 1)) * C1 + cbase;
+          uint4 pk;
+          pk.x = mtb::pack_bf16x2(__uint_as_float(f[0] & ~3u), __uint_as_float(f[1] & ~3u));
+          pk.y = mtb::pack_bf16x2(__uint_as_float(f[2] & ~3u), __uint_as_float(f[3] & ~3u));
+          pk.z = mtb::pack_bf16x2(__uint_as_float(f[4] & ~3u), __uint_as_float(f[5] & ~3u));
+          pk.w = mtb::pack_bf16x2(__uint_as_float(f[6] & ~3u), __uint_as_float(f[7] & ~3u));
+          *reinterpret_cast<uint4*>(out + o) = pk;
+          uint2 k2;
+          k2.x = (3u - (f[0] & 3u)) | ((3u - (f[1] & 3u)) << 8) | ((3u - (f[2] & 3u)) << 16) | ((3u - (f[3] & 3u)) << 24);
+          k2.y = (3u - (f[4] & 3u)) | ((3u - (f[5] & 3u)) << 8) | ((3u - (f[6] & 3u)) << 16) | ((3u - (f[7] & 3u)) << 24);
+          *reinterpret_cast<uint2*>(idx + o) = k2;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_empty[s]);
+    }
+  }
+  __syncthreads();
+  if (warp == 0) { tc_fence_after(); tmem_dealloc<512>(tmem); }
+}
+
+// ======================================================================================= wgrad
+namespace g1 {
+constexpr int kProducers = 256;                              // per stage; one producer group per stage
+constexpr int kThreads = 32 + 2 * kProducers + 128;          // warp 0 MMA, 1-16 producers, 17-20 final epilogue
+constexpr int DA_BYTES = 896 * 64;                           // [pixel row][32 c] bf16, SW64
+constexpr int kOffX5 = 0;
+constexpr int kOffDA = 2 * X5_BYTES;                         // 59392 (1 KiB aligned)
+constexpr int kOffXs = kOffDA + 2 * DA_BYTES;
+constexpr int kOffBar = kOffXs + 2 * XS_FLOATS * 4;
+constexpr int kSmem = 1024 + kOffBar + 128;
+}  // namespace g1
+
+__global__ void __launch_bounds__(g1::kThreads, 1)
+conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, const bf16* __restrict__ P,
+                      const uint8_t* __restrict__ idx, float* __restrict__ dW, float* __restrict__ db, int B) {
+  using namespace g1;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sX5 = smem + kOffX5;
+  uint8_t* sDA = smem + kOffDA;
+  float* sXs = reinterpret_cast<float*>(smem + kOffXs);
+  uint64_t* x_full = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* x_empty = x_full + 2;
+  uint64_t* a_full = x_empty + 2;
+  uint32_t* holder = reinterpret_cast<uint32_t*>(a_full + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // X5 tails and the padding columns (w >= 28) of dA must read as zero for the whole kernel
+  for (int i = threadIdx.x; i < (2 * X5_BYTES + 2 * DA_BYTES) / 16; i += kThreads)
+    reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) { mbar_init(&x_full[s], kProducers); mbar_init(&x_empty[s], 1); }
+    mbar_init(a_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<32>(holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, C1, true, true);
+      int it = 0;
+      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+        const int s = it & 1, ph = (it >> 1) & 1;
+        mbar_wait(&x_full[s], ph);
+        tc_fence_after();
+        // A: 8 atoms of 16 (kh) one kw = 4 rows = 128 bytes apart; B: one 32-channel atom
+        const uint64_t a0 = make_smem_desc(smem_u32(sX5 + s * X5_BYTES), 128, 256, kSwizzle32B);
+        const uint64_t b0 = make_smem_desc(smem_u32(sDA + s * DA_BYTES), 64, 512, kSwizzle64B);
+        if (it == 0) mma_f16_first(tmem, a0, b0, idesc);
+        else mma_f16_acc(tmem, a0, b0, idesc);
+#pragma unroll 8
+        for (int ks = 1; ks < 56; ++ks)
+          mma_f16_acc(tmem, a0 + (uint64_t)((ks * 16 * 32) >> 4), b0 + (uint64_t)((ks * 16 * 64) >> 4), idesc);
+        mma_commit(&x_empty[s]);
+      }
+      mma_commit(a_full);
+    }
+    __syncwarp();
+  } else if (warp <= 16) {
+    const int g = (warp - 1) >> 3;
+    const int t = threadIdx.x - 32 - g * kProducers;
+    float* xs = sXs + g * XS_FLOATS;
+    uint8_t* da = sDA + g * DA_BYTES;
+    int it = g;
+    for (int img = blockIdx.x + g * gridDim.x; img < B; img += 2 * gridDim.x, it += 2) {
+      const int ph = (it >> 1) & 1;
+      // all global loads of this image first: pooled gradient, pooled activation, argmax (16+16+8 bytes
+      // per 8 channels of a pooled pixel), then the padded input image
+      constexpr int PER = (196 * 4 + kProducers - 1) / kProducers;      // 4 (the last one only for t < 16)
+      uint4 gq[PER], aq[PER];
+      uint2 kq[PER];
+#pragma unroll
+      for (int k = 0; k < PER; ++k) {
+        const int item = t + k * kProducers;
+        if (item < 196 * 4) {
+          const size_t o = ((size_t)img * 196 + (item >> 2)) * C1 + (item & 3) * 8;
+          gq[k] = __ldg(reinterpret_cast<const uint4*>(dP + o));
+          aq[k] = __ldg(reinterpret_cast<const uint4*>(P + o));
+          kq[k] = __ldg(reinterpret_cast<const uint2*>(idx + o));
+        }
+      }
+      mbar_wait(&x_empty[g], ph ^ 1);
+      load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);
+      // dA rows of one pooling window: gradient goes to the argmax position if the pooled
+      // activation is positive (ReLU), the other three positions get zero
+#pragma unroll
+      for (int k = 0; k < PER; ++k) {
+        const int item = t + k * kProducers;
+        if (item < 196 * 4) {
+          const int pp = item >> 2, chunk = item & 3;
+          const int ph2 = pp / 14, pw = pp % 14;
+          const uint32_t gw[4] = {gq[k].x, gq[k].y, gq[k].z, gq[k].w}, aw[4] = {aq[k].x, aq[k].y, aq[k].z, aq[k].w};
+          uint32_t kk[8];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) { kk[e] = (kq[k].x >> (8 * e)) & 0xff; kk[4 + e] = (kq[k].y >> (8 * e)) & 0xff; }
+          uint32_t gm[4];                                    // gradient with the ReLU mask applied, bf16x2
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 av = mtb::unpack_bf16x2(aw[e]);
+            gm[e] = gw[e] & ((av.x > 0.f ? 0x0000ffffu : 0u) | (av.y > 0.f ? 0xffff0000u : 0u));
+          }
+#pragma unroll
+          for (int pos = 0; pos < 4; ++pos) {
+            uint4 v;
+            uint32_t o4[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              o4[e] = gm[e] & ((kk[2 * e] == (uint32_t)pos ? 0x0000ffffu : 0u) |
+                               (kk[2 * e + 1] == (uint32_t)pos ? 0xffff0000u : 0u));
+            v.x = o4[0]; v.y = o4[1]; v.z = o4[2]; v.w = o4[3];
+            const int h = 2 * ph2 + (pos >> 1), wc = 2 * pw + (pos & 1);
+            const int R = (h >> 2) * 128 + wc * 4 + (h & 3);
+            *reinterpret_cast<uint4*>(da + R * 64 + ((chunk ^ ((R >> 1) & 3)) << 4)) = v;
+          }
+        }
+      }
+      named_bar(2 + g, kProducers);                          // padded image complete
+      build_x5(sX5 + g * X5_BYTES, xs, t, kProducers);
+      fence_proxy_async_smem();
+      mbar_arrive(&x_full[g]);
+      named_bar(2 + g, kProducers);                          // everyone is done reading xs
+    }
+  } else {
+    const int q = warp & 3;
+    const int L = q * 32 + lane;
+    const int kw = L >> 4, kh = L & 15;
+    if (blockIdx.x < B) {
+      mbar_wait(a_full, 0);
+      tc_fence_after();
+      uint32_t r[32];
+      tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16), r);
+      tmem_ld_wait();
+      if (kw < 5 && kh < 5) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) atomicAdd(dW + (kh * 5 + kw) * C1 + c, __uint_as_float(r[c]));
+      } else if (kw == 0 && kh == 5) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) atomicAdd(db + c, __uint_as_float(r[c]));
+      }
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 0) { tc_fence_after(); tmem_dealloc<32>(tmem); }
+}
+
+template <typename K>
+int set_smem(K kern, int bytes, bool* done) {
+  if (!*done) {
+    MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    *done = true;
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Tensor-core versions of mtb_conv1_fwd / mtb_conv1_wgrad (same arguments and output formats), C1 = 32.
+int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                     cudaStream_t stream) {
+  MTB_REQUIRE(x && w && bias && out_bf16 && idx && B > 0, "conv1_fwd_tc: bad argument");
+  static bool attr = false;
+  if (int e = set_smem(conv1_fwd_tc_kernel, f1::kSmem, &attr)) return e;
+  const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
+  conv1_fwd_tc_kernel<<<grid, f1::kThreads, f1::kSmem, stream>>>(x, w, bias, reinterpret_cast<bf16*>(out_bf16), idx, B);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+// dW and db are ACCUMULATED into (caller zeroes them once per step).
+int mtb_conv1_wgrad_tc(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
+                       int B, cudaStream_t stream) {
+  MTB_REQUIRE(x && dP_bf16 && P_bf16 && idx && dW && db && B > 0, "conv1_wgrad_tc: bad argument");
+  static bool attr = false;
+  if (int e = set_smem(conv1_wgrad_tc_kernel, g1::kSmem, &attr)) return e;
+  const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
+  conv1_wgrad_tc_kernel<<<grid, g1::kThreads, g1::kSmem, stream>>>(x, reinterpret_cast<const bf16*>(dP_bf16),
+                                                                  reinterpret_cast<const bf16*>(P_bf16), idx, dW, db, B);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

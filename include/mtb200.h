@@ -67,6 +67,12 @@ int mtb_conv1_fwd(const float* x, const float* w, const float* bias, void* out_b
 int mtb_conv1_wgrad(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
                     int B, int C1, cudaStream_t stream);
 
+/* tensor-core versions for C1 == 32 (csrc/conv1_sm100.cu): same arguments minus C1, same output formats */
+int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                     cudaStream_t stream);
+int mtb_conv1_wgrad_tc(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
+                       int B, cudaStream_t stream);
+
 /* ---- pooling + generic-conv helpers (mpipy.py:158,161; tf.nn.conv2d mpipy.py:159 via im2col) ---- */
 int mtb_maxpool2x2_fwd(const void* in, void* out, uint8_t* idx, int B, int H, int W, int C, cudaStream_t stream);
 int mtb_unpool_relu_bwd(const void* dP, const void* P, const uint8_t* idx, void* dA, int B, int H, int W, int C,

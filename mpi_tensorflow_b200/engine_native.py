@@ -112,6 +112,8 @@ class NativeEngine:
         self.dh, self.dflat = z(Bmax, s.fc), z(Bmax, s.flat_dim)
         self.da2 = z(Bmax, 14, 14, s.c2)
         self.dp1 = z(Bmax, 14, 14, s.c1)
+        # conv1 on tensor cores when it has 32 output channels, else the CUDA-core kernel
+        self.conv1_tc = s.c1 == 32 and self.conv_impl != "im2col"
         # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
         want = self.conv_impl
         have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2))
@@ -206,8 +208,12 @@ class NativeEngine:
         P, S = self.P, self.S
         keep = s.keep_prob if (train and c.dropout) else 1.0
         # conv1 + bias + ReLU + pool (mpipy.py:156-158)
-        N.call("mtb_conv1_fwd", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
-               self.a1p.data_ptr(), self.idx1.data_ptr(), B, s.c1)
+        if self.conv1_tc:
+            N.call("mtb_conv1_fwd_tc", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(),
+                   P["conv1_bias"].data_ptr(), self.a1p.data_ptr(), self.idx1.data_ptr(), B)
+        else:
+            N.call("mtb_conv1_fwd", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
+                   self.a1p.data_ptr(), self.idx1.data_ptr(), B, s.c1)
         # conv2 + bias + ReLU + pool (mpipy.py:159-161)
         M2, K2 = B * 196, 25 * s.c1
         if self.conv2_implicit:
@@ -264,8 +270,12 @@ class NativeEngine:
             N.gemm_bf16(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
             N.call("mtb_col2im_5x5", self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
         # pool1 + ReLU backward fused into the conv1 weight gradient
-        N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
-               self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
+        if self.conv1_tc:
+            N.call("mtb_conv1_wgrad_tc", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
+                   self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B)
+        else:
+            N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
+                   self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
 
     def _zero_step_accumulators(self):
         for lo, hi in self._zero_ranges:

@@ -54,6 +54,8 @@ _SIGS = {
     "mtb_l2_half_sumsq": [vp, i64, vp, vp],
     "mtb_conv1_fwd": [vp, vp, vp, vp, vp, i32, i32, vp],
     "mtb_conv1_wgrad": [vp, vp, vp, vp, vp, vp, i32, i32, vp],
+    "mtb_conv1_fwd_tc": [vp, vp, vp, vp, vp, i32, vp],
+    "mtb_conv1_wgrad_tc": [vp, vp, vp, vp, vp, vp, i32, vp],
     "mtb_maxpool2x2_fwd": [vp, vp, vp, i32, i32, i32, i32, vp],
     "mtb_unpool_relu_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
     "mtb_im2col_5x5": [vp, vp, i32, i32, i32, i32, vp],

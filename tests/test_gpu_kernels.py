@@ -108,32 +108,45 @@ def test_gemm_dropout_matches_philox_stream(N, dev):
 
 
 # ----------------------------------------------------------------------------- conv1
-@pytest.mark.parametrize("B,C1", [(3, 32), (70, 32), (5, 128)])
-def test_conv1_fwd_and_wgrad(N, dev, B, C1):
+@pytest.mark.parametrize("B,C1,tc", [(3, 32, False), (70, 32, False), (5, 128, False), (1, 32, True), (7, 32, True),
+                                       (150, 32, True), (299, 32, True)])
+def test_conv1_fwd_and_wgrad(N, dev, B, C1, tc):
+    """CUDA-core (any C1) and tensor-core (C1 = 32, bf16 operands) versions against the fp32 oracle."""
     x = (torch.rand(B, 28, 28) - 0.5).to(dev)
     w = (torch.randn(5, 5, 1, C1) * 0.1).to(dev)
     bias = (torch.randn(C1) * 0.1).to(dev)
     out = torch.zeros(B, 14, 14, C1, dtype=torch.bfloat16, device=dev)
-    idx = torch.zeros(B, 14, 14, C1, dtype=torch.uint8, device=dev)
-    N.call("mtb_conv1_fwd", x.data_ptr(), w.data_ptr(), bias.data_ptr(), out.data_ptr(), idx.data_ptr(), B, C1)
+    idx = torch.full((B, 14, 14, C1), 9, dtype=torch.uint8, device=dev)
+    if tc:
+        N.call("mtb_conv1_fwd_tc", x.data_ptr(), w.data_ptr(), bias.data_ptr(), out.data_ptr(), idx.data_ptr(), B)
+    else:
+        N.call("mtb_conv1_fwd", x.data_ptr(), w.data_ptr(), bias.data_ptr(), out.data_ptr(), idx.data_ptr(), B, C1)
     torch.cuda.synchronize()
     xr = x.cpu().reshape(B, 28, 28, 1)
-    a = torch.relu(O.conv5x5(xr, w.cpu()) + bias.cpu())
+    if tc:      # the tensor-core kernel multiplies bf16-rounded pixels and weights
+        a = torch.relu(O.conv5x5(O.bf16_round(xr), O.bf16_round(w.cpu())) + bias.cpu())
+    else:
+        a = torch.relu(O.conv5x5(xr, w.cpu()) + bias.cpu())
     p, i = O.maxpool2x2(a)
     assert float((out.cpu().float() - p).abs().max()) < 1e-2 * max(1.0, float(p.abs().max()))
     # argmax may differ only where two window entries tie numerically
     agree = (idx.cpu().long() == i.long()).float().mean()
     assert agree > 0.999
+    assert int(idx.max()) <= 3
     # wgrad: gradient of sum(dP * pool(relu(conv))) w.r.t. w and bias
     dP = _bf(torch.randn(B, 14, 14, C1)).to(dev)
     dW = torch.zeros(25, C1, device=dev)
     db = torch.zeros(C1, device=dev)
-    N.call("mtb_conv1_wgrad", x.data_ptr(), dP.data_ptr(), out.data_ptr(), idx.data_ptr(), dW.data_ptr(),
-           db.data_ptr(), B, C1)
+    if tc:
+        N.call("mtb_conv1_wgrad_tc", x.data_ptr(), dP.data_ptr(), out.data_ptr(), idx.data_ptr(), dW.data_ptr(),
+               db.data_ptr(), B)
+    else:
+        N.call("mtb_conv1_wgrad", x.data_ptr(), dP.data_ptr(), out.data_ptr(), idx.data_ptr(), dW.data_ptr(),
+               db.data_ptr(), B, C1)
     torch.cuda.synchronize()
     g = dP.cpu().float() * (out.cpu().float() > 0).float()
     da = O.maxpool2x2_bwd(g, idx.cpu().long())
-    ref_dw = O.conv5x5_wgrad(xr, da).reshape(25, C1)
+    ref_dw = O.conv5x5_wgrad(O.bf16_round(xr) if tc else xr, da).reshape(25, C1)
     ref_db = da.sum((0, 1, 2))
     assert _rel(dW.cpu(), ref_dw) < 1e-4
     assert _rel(db.cpu(), ref_db) < 1e-4
