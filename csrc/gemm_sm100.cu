@@ -138,7 +138,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   const uint32_t tmem_base = *tmem_holder;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       for (int i = 0; i < nkb; ++i) {
         const int s = i % S, ph = (i / S) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
@@ -162,23 +162,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kFmtBF16, BM, BN, A_MN, B_MN);
+      // one descriptor per operand; stages and K steps only move the 14-bit start-address field
+      const uint64_t da0 = A_MN ? make_smem_desc(smem_u32(sA), 8192, 1024, kSwizzle128B)
+                                : make_smem_desc(smem_u32(sA), 16, 1024, kSwizzle128B);
+      const uint64_t db0 = B_MN ? make_smem_desc(smem_u32(sB), 8192, 1024, kSwizzle128B)
+                                : make_smem_desc(smem_u32(sB), 16, 1024, kSwizzle128B);
+      constexpr uint32_t a_kstep = (A_MN ? 2048 : 32) >> 4, b_kstep = (B_MN ? 2048 : 32) >> 4;
+      int s = 0, ph = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % S, ph = (i / S) & 1;
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(sA + s * C::kABytes);
-        const uint32_t b_base = smem_u32(sB + s * C::kBBytes);
+        const uint64_t da = da0 + (uint64_t)((uint32_t)(s * C::kABytes) >> 4);
+        const uint64_t db = db0 + (uint64_t)((uint32_t)(s * C::kBBytes) >> 4);
+        if (i == 0) mma_f16_first(tmem_base, da, db, idesc);
+        else mma_f16_acc(tmem_base, da, db, idesc);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t da = A_MN ? make_smem_desc(a_base + k * 2048, 8192, 1024, kSwizzle128B)
-                                   : make_smem_desc(a_base + k * 32, 16, 1024, kSwizzle128B);
-          const uint64_t db = B_MN ? make_smem_desc(b_base + k * 2048, 8192, 1024, kSwizzle128B)
-                                   : make_smem_desc(b_base + k * 32, 16, 1024, kSwizzle128B);
-          mma_f16(tmem_base, da, db, idesc, (i | k) != 0);
-        }
+        for (int k = 1; k < BK / 16; ++k) mma_f16_acc(tmem_base, da + k * a_kstep, db + k * b_kstep, idesc);
         mma_commit(&empty_bar[s]);       // smem slot reusable once these MMAs retire
+        if (++s == S) { s = 0; ph ^= 1; }
       }
       mma_commit(tmem_full);             // accumulator complete
     }

@@ -17,6 +17,7 @@ fp32 master weights, optimizer state and gradients.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Optional
 
 import numpy as np
@@ -229,7 +230,7 @@ class NativeEngine:
         flat = self.a2p.view(self.Bmax, s.flat_dim)
         N.gemm_bf16(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
                     keep_prob=keep, seed=c.seed, step_ptr=self.dev_step,
-                    bn=64 if B * s.fc < 96 * 128 * 128 else 128)
+                    bn=int(os.environ.get("MTB_FC1_BN", "0")) or (64 if B * s.fc < 96 * 128 * 128 else 128))
         # FC2 + softmax + CE + dlogits (mpipy.py:167, :55-56, :67)
         N.call("mtb_fc2_softmax_ce", self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
                self.y_in.data_ptr() if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
