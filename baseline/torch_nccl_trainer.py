@@ -48,7 +48,9 @@ class Step:
     def __init__(self, model, batch, rows, world, dev, optimizer="momentum", graph=True, seed=1):
         torch.manual_seed(seed)
         c1, c2, fc, keep = PRESETS[model]
-        self.net = MnistCnn(c1, c2, fc, keep).to(dev).to(memory_format=torch.channels_last)
+        self.net = MnistCnn(c1, c2, fc, keep).to(dev)
+        if os.environ.get("BASELINE_CHANNELS_LAST", "0") == "1":
+            self.net = self.net.to(memory_format=torch.channels_last)
         self.world, self.B, self.rows, self.dev = world, batch, rows, dev
         params = list(self.net.parameters())
         # one flat gradient buffer -> one NCCL all_reduce per step
@@ -73,6 +75,7 @@ class Step:
         self.y = torch.zeros(batch, dtype=torch.int64, device=dev)
         self.loss = torch.zeros((), device=dev)
         self.graph = None
+        self.graph_nowin = None
         self.use_graph = graph
         self.idx = torch.arange(batch, device=dev)
 
@@ -134,6 +137,10 @@ class Step:
 
 
 def bench(args, metric, ClockSampler, physical_gpu_index) -> dict:
+    if os.environ.get("BASELINE_DEBUG"):
+        import faulthandler
+        import sys
+        faulthandler.dump_traceback_later(int(os.environ["BASELINE_DEBUG"]), exit=True, file=sys.stderr)
     n = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -194,6 +201,9 @@ def bench(args, metric, ClockSampler, physical_gpu_index) -> dict:
            "clocks": sampler.summary(), "gpu_launches": 0}
     if e2e:
         out["e2e"] = e2e
-    if n > 1:
-        dist.destroy_process_group()
+    # graphs that captured NCCL work keep the communicator busy: drop them and skip the explicit
+    # destroy (it blocks forever here); the caller prints the result and exits the process
+    st.graph = None
+    st.graph_nowin = None
+    torch.cuda.synchronize()
     return out if rank == 0 else {}

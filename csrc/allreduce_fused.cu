@@ -32,7 +32,7 @@ namespace {
 using namespace mtb;
 
 constexpr int kMaxRanks = 16;
-constexpr int kMaxBlocks = 256;
+constexpr int kMaxBlocks = 512;
 constexpr int kMaxRanges = 8;
 constexpr long long kSpinLimit = 30000000000ll;     // ~15 s at 2 GHz
 
@@ -58,6 +58,8 @@ struct FusedParams {
   float momentum, beta1, beta2, eps, wd;
   int n_ranges;
   long long range_begin[kMaxRanges], range_end[kMaxRanges];   // where the L2 term applies
+  long long* advance_step;                          // bumped by the last block to finish (may be null)
+  unsigned int* done_counter;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -175,10 +177,11 @@ __device__ __forceinline__ uint2 to_bf16x4(float4 w) {
   return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
 }
 
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(256)
 fused_allreduce_update_kernel(const FusedParams p) {
   const int b = blockIdx.x;
   __shared__ uint32_t s_seq;
+  pdl_sync();
   if (threadIdx.x == 0) s_seq = p.seq[b];
   __syncthreads();
   const uint32_t seq = s_seq;
@@ -240,7 +243,17 @@ fused_allreduce_update_kernel(const FusedParams p) {
     }
   }
   if (multi) cross_gpu_barrier(p, b, seq + 2);       // peers are done reading my grads / writing my params
-  if (threadIdx.x == 0) p.seq[b] = seq + 2;
+  if (threadIdx.x == 0) {
+    p.seq[b] = seq + 2;
+    if (p.advance_step != nullptr) {
+      // every block read the step counter at its start; the last one to finish moves it on
+      __threadfence();
+      if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
+        *p.done_counter = 0u;
+        *p.advance_step += 1;
+      }
+    }
+  }
 }
 
 __global__ void barrier_kernel(const FusedParams p) {
@@ -284,6 +297,9 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->momentum = a->momentum; p->beta1 = a->beta1; p->beta2 = a->beta2; p->eps = a->eps; p->wd = a->wd;
   p->n_ranges = a->n_ranges;
   for (int r = 0; r < kMaxRanges; ++r) { p->range_begin[r] = a->range_begin[r]; p->range_end[r] = a->range_end[r]; }
+  p->advance_step = reinterpret_cast<long long*>(a->advance_step);
+  p->done_counter = reinterpret_cast<unsigned int*>(a->done_counter);
+  MTB_REQUIRE(p->advance_step == nullptr || p->done_counter != nullptr, "fused: advance_step needs done_counter");
   return 0;
 }
 
@@ -296,16 +312,17 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   MTB_REQUIRE(p.world == 1 || (p.seq && p.status && p.flags[p.rank]), "fused: multi-GPU needs flags/seq/status");
   MTB_REQUIRE(p.seq, "fused: seq buffer required");
   if (p.count == 0) return 0;
-  int block = a->block > 0 ? a->block : 512;
+  // 256-thread blocks without shared memory fit next to the persistent tensor-core kernels, so
+  // a bucket's update can run on a second stream underneath the rest of backward
+  int block = a->block > 0 ? (a->block > 256 ? 256 : a->block) : 256;
   long long vecs = p.count >> 2;
   if (p.world > 1 && p.algo != 0) vecs = (vecs + p.world - 1) / p.world;
-  int grid = a->grid > 0 ? a->grid : 148;
+  int grid = a->grid > 0 ? a->grid : 3 * 148;
   long long need = (vecs + block - 1) / block;
   if (need < 1) need = 1;
   if (grid > need) grid = (int)need;
   if (grid > kMaxBlocks) grid = kMaxBlocks;
-  fused_allreduce_update_kernel<<<grid, block, 0, stream>>>(p);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(fused_allreduce_update_kernel, dim3(grid), dim3(block), 0, stream, p));
   return 0;
 }
 

@@ -27,6 +27,36 @@ namespace mtb {
 
 constexpr int kNumSMs = 148;
 
+// ---- programmatic dependent launch -------------------------------------------------------------
+// Every kernel of the training step is launched with the programmatic-stream-serialization
+// attribute and calls pdl_sync() once, by all threads, after the part of its prologue that
+// touches no global data (barrier init, TMEM allocation, shared-memory clears, tensor-map
+// prefetch).  The next kernel's CTAs can then be placed, and run that prologue, while this
+// kernel's tail is still executing; pdl_sync() returns only when the previous kernel has
+// completed and its writes are visible, so everything after it sees the usual stream order.
+__device__ __forceinline__ void pdl_sync() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+bool pdl_enabled();      // MTB_PDL=0 turns the launch attribute off (runtime.cu)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                          Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // ---- Philox4x32-10: identical to utils/philox.py ------------------------------

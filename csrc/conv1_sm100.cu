@@ -96,19 +96,8 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
   uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // zero both X5 stages (tail rows and padding stay zero for the kernel's lifetime), build weights
+  // zero both X5 stages (tail rows and padding stay zero for the kernel's lifetime)
   for (int i = threadIdx.x; i < 2 * X5_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(sX5)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = threadIdx.x; i < 5 * C1; i += kThreads) {
-    const int kw = i / C1, c = i % C1;
-    uint4 v;
-    v.x = mtb::pack_bf16x2(__ldg(w + (0 * 5 + kw) * C1 + c), __ldg(w + (1 * 5 + kw) * C1 + c));
-    v.y = mtb::pack_bf16x2(__ldg(w + (2 * 5 + kw) * C1 + c), __ldg(w + (3 * 5 + kw) * C1 + c));
-    v.z = mtb::pack_bf16x2(__ldg(w + (4 * 5 + kw) * C1 + c), 0.f);
-    v.w = 0u;
-    const int sw = (c >> 2) & 1;
-    *reinterpret_cast<uint4*>(sW + kw * 1024 + c * 32 + (sw << 4)) = v;
-    *reinterpret_cast<uint4*>(sW + kw * 1024 + c * 32 + ((sw ^ 1) << 4)) = make_uint4(0, 0, 0, 0);
-  }
   fence_proxy_async_smem();
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
@@ -124,6 +113,21 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
+  mtb::pdl_sync();
+  // per-kw weight tiles [32 c][16 kh] (K-major, SW32) from the fp32 master weights
+  for (int i = threadIdx.x; i < 5 * C1; i += kThreads) {
+    const int kw = i / C1, c = i % C1;
+    uint4 v;
+    v.x = mtb::pack_bf16x2(__ldg(w + (0 * 5 + kw) * C1 + c), __ldg(w + (1 * 5 + kw) * C1 + c));
+    v.y = mtb::pack_bf16x2(__ldg(w + (2 * 5 + kw) * C1 + c), __ldg(w + (3 * 5 + kw) * C1 + c));
+    v.z = mtb::pack_bf16x2(__ldg(w + (4 * 5 + kw) * C1 + c), 0.f);
+    v.w = 0u;
+    const int sw = (c >> 2) & 1;
+    *reinterpret_cast<uint4*>(sW + kw * 1024 + c * 32 + (sw << 4)) = v;
+    *reinterpret_cast<uint4*>(sW + kw * 1024 + c * 32 + ((sw ^ 1) << 4)) = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -275,6 +279,7 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
+  mtb::pdl_sync();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -405,8 +410,8 @@ int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* ou
   static bool attr = false;
   if (int e = set_smem(conv1_fwd_tc_kernel, f1::kSmem, &attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
-  conv1_fwd_tc_kernel<<<grid, f1::kThreads, f1::kSmem, stream>>>(x, w, bias, reinterpret_cast<bf16*>(out_bf16), idx, B);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(conv1_fwd_tc_kernel, dim3(grid), dim3(f1::kThreads), (size_t)f1::kSmem, stream, x, w, bias,
+                             reinterpret_cast<bf16*>(out_bf16), idx, B));
   return 0;
 }
 
@@ -417,9 +422,9 @@ int mtb_conv1_wgrad_tc(const float* x, const void* dP_bf16, const void* P_bf16, 
   static bool attr = false;
   if (int e = set_smem(conv1_wgrad_tc_kernel, g1::kSmem, &attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
-  conv1_wgrad_tc_kernel<<<grid, g1::kThreads, g1::kSmem, stream>>>(x, reinterpret_cast<const bf16*>(dP_bf16),
-                                                                  reinterpret_cast<const bf16*>(P_bf16), idx, dW, db, B);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(conv1_wgrad_tc_kernel, dim3(grid), dim3(g1::kThreads), (size_t)g1::kSmem, stream, x,
+                             reinterpret_cast<const bf16*>(dP_bf16), reinterpret_cast<const bf16*>(P_bf16), idx, dW, db,
+                             B));
   return 0;
 }
 

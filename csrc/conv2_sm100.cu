@@ -79,7 +79,6 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   float* sBias = reinterpret_cast<float*>(smem + kOffBar + 128);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (threadIdx.x < COUT) sBias[threadIdx.x] = __ldg(bias + threadIdx.x);
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_w);
@@ -93,6 +92,9 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
+  mtb::pdl_sync();
+  if (warp >= 2 && threadIdx.x - 64 < COUT) sBias[threadIdx.x - 64] = __ldg(bias + threadIdx.x - 64);
+  if (warp >= 2) epi_bar256();                       // bias visible to all epilogue warps
 
   if (warp == 0) {
     if (lane == 0) {
@@ -263,6 +265,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
+  mtb::pdl_sync();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -398,6 +401,7 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
+  mtb::pdl_sync();
   // CTA group j = blockIdx % 3 owns filter rows kh_j (TMEM lanes 64..127) and kh_j + 2 (lanes 0..63),
   // kh_j = 0, 1, 4, over a third of the CTAs each: three times fewer per-CTA partial sums to
   // write and reduce than letting every CTA hold all 25 taps.
@@ -500,6 +504,7 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 //   kh 0,1,4 -> group 0,1,2, lane 64+co   |   kh 2,3 -> group 0,1, lane co
 __global__ void __launch_bounds__(256)
 conv2_wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dW, int n_cta) {
+  mtb::pdl_sync();
   const int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= TAPS * CIN * COUT) return;
   const int co = o % COUT, ci = (o / COUT) % CIN, tap = o / (COUT * CIN);
@@ -583,9 +588,8 @@ int mtb_conv2_fprop_pool(const void* x_bf16, const void* w_bf16, const float* bi
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&mw, w_bf16, 0, 3), "conv2_fprop: tensor map encode failed");
   static bool attr = false;
   if (int e = set_smem(conv2_fprop_pool_kernel, fp::kSmem, &attr)) return e;
-  conv2_fprop_pool_kernel<<<grid_for(B), fp::kThreadsFp, fp::kSmem, stream>>>(mx, mw, bias, reinterpret_cast<bf16*>(out_bf16),
-                                                                       idx, B);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(conv2_fprop_pool_kernel, dim3(grid_for(B)), dim3(fp::kThreadsFp), (size_t)fp::kSmem, stream,
+                             mx, mw, bias, reinterpret_cast<bf16*>(out_bf16), idx, B));
   return 0;
 }
 
@@ -595,8 +599,8 @@ int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int 
   MTB_REQUIRE(get_map(&md, dy_bf16, B, 1) && get_map(&mw, w_bf16, 0, 3), "conv2_dgrad: tensor map encode failed");
   static bool attr = false;
   if (int e = set_smem(conv2_dgrad_kernel, dg::kSmem, &attr)) return e;
-  conv2_dgrad_kernel<<<grid_for(B), kThreads, dg::kSmem, stream>>>(md, mw, reinterpret_cast<bf16*>(dx_bf16), B);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel, dim3(grid_for(B)), dim3(kThreads), (size_t)dg::kSmem, stream, md, mw,
+                             reinterpret_cast<bf16*>(dx_bf16), B));
   return 0;
 }
 
@@ -612,11 +616,10 @@ int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* d
   static bool attr = false;
   if (int e = set_smem(conv2_wgrad_kernel, wg::kSmem, &attr)) return e;
   const int grid = wgrad_grid(B);
-  conv2_wgrad_kernel<<<grid, kThreads, wg::kSmem, stream>>>(mx, md, reinterpret_cast<float*>(workspace), db, B);
-  MTB_LAUNCH_CHECK();
-  conv2_wgrad_reduce_kernel<<<(TAPS * CIN * COUT + 255) / 256, 256, 0, stream>>>(
-      reinterpret_cast<const float*>(workspace), dW, grid);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_kernel, dim3(grid), dim3(kThreads), (size_t)wg::kSmem, stream, mx, md,
+                             reinterpret_cast<float*>(workspace), db, B));
+  MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_reduce_kernel, dim3((TAPS * CIN * COUT + 255) / 256), dim3(256), 0, stream,
+                             reinterpret_cast<const float*>(workspace), dW, grid));
   return 0;
 }
 

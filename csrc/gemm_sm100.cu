@@ -136,6 +136,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
+  mtb::pdl_sync();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -292,8 +293,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
     attr_set = true;
   }
   dim3 grid((unsigned)mtb::ceil_div(p.M, BM), (unsigned)mtb::ceil_div(p.N, BN), (unsigned)p.splits);
-  kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, st>>>(ma, mb, p);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(kern, grid, dim3(kThreads), (size_t)Cfg<BN>::kSmemBytes, st, ma, mb, p));
   return 0;
 }
 

@@ -133,9 +133,211 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
   atomicAdd(out + c, acc);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Faster variants used by the engine.
+//
+// Forward: 32 rows per block, lane <-> row, the 8 warps split the features; W sits in shared
+// memory and every read of it is a warp-wide broadcast, so the loop is pure FMA.  Loss and error
+// count are reduced inside the block first: one atomic per block instead of one per row.
+template <int NC>
+__global__ void __launch_bounds__(256)
+fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
+                           const float* __restrict__ bias, const int* __restrict__ labels, float* __restrict__ logits,
+                           float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ loss_accum,
+                           int* __restrict__ err_accum, int B, int F) {
+  extern __shared__ float sm[];
+  pdl_sync();
+  float* sW = sm;                                      // [F][NC]
+  float* red = sm + (size_t)F * NC;                    // [8 warps][NC][32 rows]
+  {
+    const float4* src = reinterpret_cast<const float4*>(W);
+    float4* dst = reinterpret_cast<float4*>(sW);
+    for (int i = threadIdx.x; i < F * NC / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 32 + lane;
+  const int fper = F / 8, fbeg = warp * fper;
+  float acc[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) acc[c] = 0.f;
+  if (row < B) {
+    const uint4* hr = reinterpret_cast<const uint4*>(h + (size_t)row * F + fbeg);
+#pragma unroll 4
+    for (int i = 0; i < fper / 8; ++i) {
+      const uint4 pk = __ldg(hr + i);
+      const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
+      const float* wr = sW + (size_t)(fbeg + i * 8) * NC;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 hv = unpack_bf16x2(w4[e]);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          acc[c] = fmaf(hv.x, wr[(2 * e) * NC + c], acc[c]);
+          acc[c] = fmaf(hv.y, wr[(2 * e + 1) * NC + c], acc[c]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NC; ++c) red[(warp * NC + c) * 32 + lane] = acc[c];
+  __syncthreads();
+  if (warp != 0) return;
+  float lg[NC];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    float s = __ldg(bias + c);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[(w * NC + c) * 32 + lane];
+    lg[c] = s;
+    mx = fmaxf(mx, s);
+  }
+  float s = 0.f, e[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) { e[c] = expf(lg[c] - mx); s += e[c]; }
+  const float inv = 1.0f / s, invB = 1.0f / (float)B;
+  const bool valid = row < B;
+  const int y = (labels && valid) ? labels[row] : -1;
+  int arg = 0;
+  float best = -INFINITY, ly = 0.f;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    if (lg[c] > best) { best = lg[c]; arg = c; }
+    if (c == y) ly = lg[c];
+  }
+  if (valid) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const float p = e[c] * inv;
+      if (logits) logits[(size_t)row * NC + c] = lg[c];
+      if (probs) probs[(size_t)row * NC + c] = p;
+      if (dlogits) dlogits[(size_t)row * NC + c] = (p - (c == y ? 1.f : 0.f)) * invB;
+    }
+  }
+  float l = (valid && y >= 0) ? -(ly - mx - logf(s)) * invB : 0.f;
+  l = warp_sum(l);
+  const unsigned wrong = __ballot_sync(0xffffffffu, valid && y >= 0 && arg != y);
+  if (lane == 0) {
+    if (loss_accum && labels) atomicAdd(loss_accum, l);
+    if (err_accum && wrong) atomicAdd(err_accum, __popc(wrong));
+  }
+}
+
+// Backward of FC2 in one pass over h: weight gradient, bias gradient, input gradient with the
+// dropout/ReLU mask, and the column sums of that input gradient (= FC1's bias gradient).
+//   grid (F/64, splits), 256 threads: lane <-> 2 features, warps and blockIdx.y split the rows.
+template <int NC>
+__global__ void __launch_bounds__(256)
+fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ dlogits,
+                     const float* __restrict__ W /*[F,NC]*/, __nv_bfloat16* __restrict__ dh, float* __restrict__ dW,
+                     float* __restrict__ db2, float* __restrict__ db1, int B, int F, float scale, int rows_per_block) {
+  extern __shared__ float sm[];                        // dl [rows_per_block][NC], then the reduction buffer
+  pdl_sync();
+  float* sdl = sm;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int f0 = blockIdx.x * 64 + lane * 2;
+  const int b0 = blockIdx.y * rows_per_block;
+  const int nrows = min(rows_per_block, B - b0);
+  for (int i = threadIdx.x; i < nrows * NC; i += blockDim.x) sdl[i] = dlogits[(size_t)b0 * NC + i];
+  float w0[NC], w1[NC], a0[NC], a1[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    w0[c] = f0 < F ? __ldg(W + (size_t)f0 * NC + c) : 0.f;
+    w1[c] = f0 + 1 < F ? __ldg(W + (size_t)(f0 + 1) * NC + c) : 0.f;
+    a0[c] = 0.f; a1[c] = 0.f;
+  }
+  float cs0 = 0.f, cs1 = 0.f;
+  __syncthreads();
+  if (f0 < F) {
+    for (int r = warp; r < nrows; r += 8) {
+      const float* dl = sdl + r * NC;
+      const size_t o = (size_t)(b0 + r) * F + f0;
+      const float2 hv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + o));
+      float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        const float d = dl[c];
+        t0 = fmaf(d, w0[c], t0);
+        t1 = fmaf(d, w1[c], t1);
+        a0[c] = fmaf(hv.x, d, a0[c]);
+        a1[c] = fmaf(hv.y, d, a1[c]);
+      }
+      t0 = hv.x > 0.f ? t0 * scale : 0.f;
+      t1 = hv.y > 0.f ? t1 * scale : 0.f;
+      const __nv_bfloat162 q = __floats2bfloat162_rn(t0, t1);
+      *reinterpret_cast<__nv_bfloat162*>(dh + o) = q;
+      const float2 qf = __bfloat1622float2(q);           // bias gradient of FC1 sums what FC1's wgrad will see
+      cs0 += qf.x;
+      cs1 += qf.y;
+    }
+  }
+  __syncthreads();                                      // everyone is done with sdl
+  float* red = sm;                                      // [8 warps][2*NC+2][32 lanes]
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    red[(warp * (2 * NC + 2) + c) * 32 + lane] = a0[c];
+    red[(warp * (2 * NC + 2) + NC + c) * 32 + lane] = a1[c];
+  }
+  red[(warp * (2 * NC + 2) + 2 * NC) * 32 + lane] = cs0;
+  red[(warp * (2 * NC + 2) + 2 * NC + 1) * 32 + lane] = cs1;
+  __syncthreads();
+  for (int i = threadIdx.x; i < (2 * NC + 2) * 32; i += blockDim.x) {
+    const int k = i >> 5, l = i & 31;
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[(w * (2 * NC + 2) + k) * 32 + l];
+    const int f = blockIdx.x * 64 + l * 2;
+    if (f >= F) continue;
+    if (k < NC) atomicAdd(dW + (size_t)f * NC + k, s);
+    else if (k < 2 * NC) { if (f + 1 < F) atomicAdd(dW + (size_t)(f + 1) * NC + (k - NC), s); }
+    else if (k == 2 * NC) atomicAdd(db1 + f, s);
+    else if (f + 1 < F) atomicAdd(db1 + f + 1, s);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < NC) {            // FC2 bias gradient: column sums of dlogits
+    float s = 0.f;
+    for (int r = 0; r < nrows; ++r) s += dlogits[(size_t)(b0 + r) * NC + threadIdx.x];
+    atomicAdd(db2 + threadIdx.x, s);
+  }
+}
+
 }  // namespace
 
 extern "C" {
+
+int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
+                            float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
+                            cudaStream_t stream) {
+  MTB_REQUIRE(NC == 10 && F % 64 == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 64");
+  const int smem = (F * NC + 8 * NC * 32) * (int)sizeof(float);
+  MTB_REQUIRE(smem <= 200 * 1024, "fc2_softmax_ce_fast: weight matrix does not fit in shared memory");
+  static int attr_bytes = 0;
+  if (smem > attr_bytes) {
+    MTB_CUDA_CHECK(cudaFuncSetAttribute(fc2_softmax_ce_rows_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_bytes = smem;
+  }
+  MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows_kernel<10>, dim3((B + 31) / 32), dim3(256), (size_t)smem, stream,
+                             reinterpret_cast<const __nv_bfloat16*>(h_bf16), W, bias, labels, logits, probs, dlogits,
+                             loss_accum, err_accum, B, F));
+  return 0;
+}
+
+// dW, db2 and db1 are accumulated into; dh is overwritten.  NC must be 10.
+int mtb_fc2_bwd_fused(const void* h_bf16, const float* dlogits, const float* W, void* dh_bf16, float* dW, float* db2,
+                      float* db1, int B, int F, int NC, float scale, cudaStream_t stream) {
+  MTB_REQUIRE(NC == 10 && F % 2 == 0, "fc2_bwd_fused: 10 classes, even F");
+  int splits = 1;
+  const int fx = (F + 63) / 64;
+  while (fx * splits < 128 && B / (splits * 2) >= 32) splits *= 2;
+  const int rows_per_block = (B + splits - 1) / splits;
+  const int smem = (int)sizeof(float) * (rows_per_block * NC > 8 * 22 * 32 ? rows_per_block * NC : 8 * 22 * 32);
+  MTB_REQUIRE(smem <= 48 * 1024, "fc2_bwd_fused: batch slice too large");
+  dim3 grid(fx, splits);
+  MTB_CUDA_CHECK(mtb::launch(fc2_bwd_fused_kernel<10>, grid, dim3(256), (size_t)smem, stream,
+                             reinterpret_cast<const __nv_bfloat16*>(h_bf16), dlogits, W,
+                             reinterpret_cast<__nv_bfloat16*>(dh_bf16), dW, db2, db1, B, F, scale, rows_per_block));
+  return 0;
+}
 
 int mtb_fc2_softmax_ce(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
                        float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,

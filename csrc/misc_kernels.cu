@@ -99,6 +99,7 @@ __global__ void l2_half_sumsq_kernel(const float* __restrict__ x, long long n, f
 __global__ void batch_window_kernel(const float4* __restrict__ data, const int* __restrict__ labels,
                                     const long long* __restrict__ step_ptr, long long rows, int B,
                                     float4* __restrict__ x_out, int* __restrict__ y_out) {
+  pdl_sync();
   const long long step = *step_ptr;
   const long long off = (step * (long long)B) % (rows - B);
   const long long n4 = (long long)B * 196;            // 784 floats = 196 float4 per image
@@ -106,6 +107,19 @@ __global__ void batch_window_kernel(const float4* __restrict__ data, const int* 
     x_out[i] = data[off * 196 + i];
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x)
     y_out[i] = labels[off + i];
+}
+
+// One launch that clears every per-step accumulator (gradient ranges whose kernels accumulate,
+// the loss and error counters): replaces a handful of separate memsets in the captured step.
+struct ZeroList { void* ptr[8]; long long n_words[8]; int count; };
+__global__ void zero_multi_kernel(const ZeroList z) {
+  pdl_sync();
+  for (int k = 0; k < z.count; ++k) {
+    uint32_t* p = reinterpret_cast<uint32_t*>(z.ptr[k]);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < z.n_words[k];
+         i += (long long)gridDim.x * blockDim.x)
+      p[i] = 0u;
+  }
 }
 
 inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + threads - 1) / threads); }
@@ -119,6 +133,20 @@ int mtb_init_trunc_normal(float* dst, long long n, float stddev, unsigned long l
   if (n <= 0) return 0;
   trunc_normal_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(dst, n, stddev, seed, stream_id);
   MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_zero_multi(void* const* ptrs, const long long* n_words, int count, cudaStream_t stream) {
+  MTB_REQUIRE(count >= 0 && count <= 8, "zero_multi: at most 8 ranges");
+  if (count == 0) return 0;
+  ZeroList z;
+  long long total = 0;
+  for (int k = 0; k < 8; ++k) { z.ptr[k] = k < count ? ptrs[k] : nullptr; z.n_words[k] = k < count ? n_words[k] : 0; total += z.n_words[k]; }
+  z.count = count;
+  unsigned blocks = blocks_for(total, 256 * 4);
+  if (blocks > 148) blocks = 148;
+  if (blocks < 1) blocks = 1;
+  MTB_CUDA_CHECK(mtb::launch(zero_multi_kernel, dim3(blocks), dim3(256), 0, stream, z));
   return 0;
 }
 
@@ -149,9 +177,9 @@ int mtb_batch_window(const float* data, const int* labels, const long long* step
   MTB_REQUIRE(rows > B && B > 0, "batch_window: shard must be larger than the batch");
   unsigned blocks = blocks_for((long long)B * 196, 256);
   if (blocks > 1184) blocks = 1184;
-  batch_window_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(data), labels, step_ptr, rows, B,
-                                                  reinterpret_cast<float4*>(x_out), y_out);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(batch_window_kernel, dim3(blocks), dim3(256), 0, stream,
+                             reinterpret_cast<const float4*>(data), labels, step_ptr, rows, B,
+                             reinterpret_cast<float4*>(x_out), y_out));
   return 0;
 }
 

@@ -53,6 +53,7 @@ __global__ void maxpool_fwd_kernel(const BF8* __restrict__ in, BF8* __restrict__
 __global__ void unpool_relu_bwd_kernel(const BF8* __restrict__ dP, const BF8* __restrict__ P,
                                        const uint2* __restrict__ idx, BF8* __restrict__ dA, long long total, int H,
                                        int W, int C8) {
+  pdl_sync();
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int c8 = (int)(i % C8);
@@ -143,11 +144,9 @@ int mtb_unpool_relu_bwd(const void* dP, const void* P, const uint8_t* idx, void*
                         cudaStream_t stream) {
   MTB_REQUIRE(C % 8 == 0 && H % 2 == 0 && W % 2 == 0, "unpool: C%8, even H/W required");
   long long total = (long long)B * (H / 2) * (W / 2) * (C / 8);
-  unpool_relu_bwd_kernel<<<nblk(total), 256, 0, stream>>>(reinterpret_cast<const BF8*>(dP),
-                                                          reinterpret_cast<const BF8*>(P),
-                                                          reinterpret_cast<const uint2*>(idx),
-                                                          reinterpret_cast<BF8*>(dA), total, H, W, C / 8);
-  MTB_LAUNCH_CHECK();
+  MTB_CUDA_CHECK(mtb::launch(unpool_relu_bwd_kernel, dim3(nblk(total)), dim3(256), 0, stream,
+                             reinterpret_cast<const BF8*>(dP), reinterpret_cast<const BF8*>(P),
+                             reinterpret_cast<const uint2*>(idx), reinterpret_cast<BF8*>(dA), total, H, W, C / 8));
   return 0;
 }
 

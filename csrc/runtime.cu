@@ -6,6 +6,7 @@
 // functions let peers map each other's arena so that collectives run as kernels
 // over NVLink instead of host-staged MPI buffers (mpipy.py:121-127).
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -28,6 +29,17 @@ int mtb_set_error_msg(int code, const char* msg, const char* file, int line) {
   g_err = buf;
   return code;
 }
+
+namespace mtb {
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("MTB_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+}  // namespace mtb
 
 extern "C" {
 

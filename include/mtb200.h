@@ -52,6 +52,7 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
 int mtb_init_trunc_normal(float* dst, long long n, float stddev, unsigned long long seed, unsigned stream_id,
                           cudaStream_t stream);
 int mtb_fill_f32(float* dst, long long n, float value, cudaStream_t stream);
+int mtb_zero_multi(void* const* ptrs, const long long* n_words, int count, cudaStream_t stream); /* <= 8 ranges of 32-bit words */
 int mtb_normalize_u8_dev(const uint8_t* src, float* dst, long long n, cudaStream_t stream);
 int mtb_synthetic_batch(float* images, int* labels, long long n_img, long long row_offset,
                         unsigned long long seed, int learnable, cudaStream_t stream);
@@ -101,6 +102,12 @@ int mtb_fc2_dgrad(const float* dlogits, const float* W, const void* h_bf16, void
                   float scale, cudaStream_t stream);
 int mtb_fc2_wgrad(const void* h_bf16, const float* dlogits, float* dW, float* db, int B, int F, int NC,
                   cudaStream_t stream);
+/* engine variants: weights staged in shared memory; one backward pass giving dW2, db2, dh and colsum(dh) = db of FC1 */
+int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
+                            float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
+                            cudaStream_t stream);
+int mtb_fc2_bwd_fused(const void* h_bf16, const float* dlogits, const float* W, void* dh_bf16, float* dW, float* db2,
+                      float* db1, int B, int F, int NC, float scale, cudaStream_t stream);
 int mtb_colsum_bf16(const void* x_bf16, float* out, long long R, int C, cudaStream_t stream);
 
 /* ---- K1: fused cross-GPU allreduce + average + L2 + optimizer + LR schedule + bf16 cast
@@ -127,6 +134,8 @@ typedef struct mtb_fused_args {
   int n_ranges;
   long long range_begin[8], range_end[8];
   int grid, block;
+  void* advance_step;   /* if set: *advance_step += 1 once every block of this launch has finished (global_step=iter_, mpipy.py:66) */
+  void* done_counter;   /* 32-bit scratch for that, zero between launches */
 } mtb_fused_args;
 int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
 int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */

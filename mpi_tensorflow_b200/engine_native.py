@@ -60,6 +60,8 @@ class NativeEngine:
         self.rows = 0
         self.decay_rows = cfg.lr_decay_rows
         self._side = torch.cuda.Stream(device=device)
+        self._comm_stream = torch.cuda.Stream(device=device)
+        self._ev_fc, self._ev_done = torch.cuda.Event(), torch.cuda.Event()
         self.last_aux: Dict = {}
 
     # ------------------------------------------------------------------ buffers
@@ -87,7 +89,9 @@ class NativeEngine:
         self.dev_step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.loss_acc = torch.zeros(1, device=dev)
         self.err_acc = torch.zeros(1, dtype=torch.int32, device=dev)
-        self._seq = torch.zeros(256, dtype=torch.int32, device=dev)
+        self._zero_args = None
+        self._done = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._seq = torch.zeros(N.lib().mtb_fused_max_blocks(), dtype=torch.int32, device=dev)
         self._status = torch.zeros(1, dtype=torch.int32, device=dev)
         self.P = {p.key: self.flat_params[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
         self.G = {p.key: self.flat_grads[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
@@ -232,27 +236,46 @@ class NativeEngine:
                     keep_prob=keep, seed=c.seed, step_ptr=self.dev_step,
                     bn=int(os.environ.get("MTB_FC1_BN", "0")) or (64 if B * s.fc < 96 * 128 * 128 else 128))
         # FC2 + softmax + CE + dlogits (mpipy.py:167, :55-56, :67)
-        N.call("mtb_fc2_softmax_ce", self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
+        N.call("mtb_fc2_softmax_ce_fast" if s.num_classes == 10 and s.fc % 64 == 0 and s.fc * 40 <= 190 * 1024 else "mtb_fc2_softmax_ce",
+               self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
                self.y_in.data_ptr() if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
                self.dlogits.data_ptr() if with_loss else None, self.loss_acc.data_ptr() if with_loss else None,
                self.err_acc.data_ptr() if with_loss else None, B, s.fc, s.num_classes)
 
     # ------------------------------------------------------------------ backward
     def _backward(self, B: int):
+        self._backward_fc(B)
+        self._backward_conv(B)
+
+    def _backward_fc(self, B: int):
+        """FC2 and FC1 backward.  When it returns, every gradient of the fc bucket is final and no
+        later kernel of the step reads an FC weight, so the bucket's fused update may start."""
         s, c = self.spec, self.cfg
         P, S, G = self.P, self.S, self.G
         scale = 1.0 / s.keep_prob if c.dropout else 1.0
         M2, K2 = B * 196, 25 * s.c1
         flat = self.a2p.view(self.Bmax, s.flat_dim)
-        N.call("mtb_fc2_wgrad", self.h.data_ptr(), self.dlogits.data_ptr(), G["fc2_weight"].data_ptr(),
-               G["fc2_bias"].data_ptr(), B, s.fc, s.num_classes)
-        N.call("mtb_fc2_dgrad", self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(), self.h.data_ptr(),
-               self.dh.data_ptr(), B, s.fc, s.num_classes, scale)
-        N.call("mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
+        if s.num_classes == 10:
+            # dW2, db2, dh (with the dropout / ReLU mask) and db of FC1 in one pass over h
+            N.call("mtb_fc2_bwd_fused", self.h.data_ptr(), self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(),
+                   self.dh.data_ptr(), G["fc2_weight"].data_ptr(), G["fc2_bias"].data_ptr(),
+                   G["fc1_bias"].data_ptr(), B, s.fc, s.num_classes, scale)
+        else:
+            N.call("mtb_fc2_wgrad", self.h.data_ptr(), self.dlogits.data_ptr(), G["fc2_weight"].data_ptr(),
+                   G["fc2_bias"].data_ptr(), B, s.fc, s.num_classes)
+            N.call("mtb_fc2_dgrad", self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(), self.h.data_ptr(),
+                   self.dh.data_ptr(), B, s.fc, s.num_classes, scale)
+            N.call("mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
+        # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand.  Runs BEFORE the
+        # weight gradient so that the last reader of the FC1 weights is done when the bucket closes.
+        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=128)
         # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket
         N.gemm_bf16(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=128)
-        # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand
-        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=128)
+
+    def _backward_conv(self, B: int):
+        s = self.spec
+        P, S, G = self.P, self.S, self.G
+        M2, K2 = B * 196, 25 * s.c1
         # pool2 + ReLU backward (O19, O18), conv2 bias gradient
         N.call("mtb_unpool_relu_bwd", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
                self.da2.data_ptr(), B, 14, 14, s.c2)
@@ -279,11 +302,14 @@ class NativeEngine:
                    self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
 
     def _zero_step_accumulators(self):
-        for lo, hi in self._zero_ranges:
-            if hi > lo:
-                self.flat_grads[lo:hi].zero_()
-        self.loss_acc.zero_()
-        self.err_acc.zero_()
+        if self._zero_args is None:
+            items = [(self.flat_grads[lo:hi].data_ptr(), hi - lo) for lo, hi in self._zero_ranges if hi > lo]
+            items += [(self.loss_acc.data_ptr(), 1), (self.err_acc.data_ptr(), 1)]
+            ptrs = (C.c_void_p * 8)(*[p for p, _ in items])
+            words = (C.c_longlong * 8)(*[n for _, n in items])
+            self._zero_args = (ptrs, words, len(items))
+        ptrs, words, n = self._zero_args
+        N.call("mtb_zero_multi", ptrs, words, n)
 
     # ------------------------------------------------------------------ update (K1)
     def _fused_args(self, peers: bool, lr_override: float = -1.0) -> N.FusedArgs:
@@ -321,12 +347,16 @@ class NativeEngine:
             return 1
         return 1 if count * 4 > (256 << 10) else 0
 
-    def _update(self, peers: bool, lr_override: float = -1.0):
+    def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
+                advance: bool = True):
+        """K1 over elements [lo, hi) of the flat buffers; ``advance`` also bumps the step counter."""
+        hi = self.n if hi is None else hi
         a = self._fused_args(peers, lr_override)
-        a.offset, a.count = 0, self.n
-        a.algo = self._pick_algo(self.n) if peers else 0
+        a.offset, a.count = lo, hi - lo
+        a.algo = self._pick_algo(hi - lo) if peers else 0
+        if advance:                                                     # iter_ += 1 in the same launch
+            a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done.data_ptr()
         N.call("mtb_fused_allreduce_update", C.byref(a))
-        N.call("mtb_advance_step", self.dev_step.data_ptr())
 
     # ------------------------------------------------------------------ engine interface
     def compute_grads(self, x, y, step: int) -> float:
@@ -363,8 +393,24 @@ class NativeEngine:
     def _step_body(self):
         self._zero_step_accumulators()
         self._forward(self.B, True, True)
-        self._backward(self.B)
-        self._update(peers=True)
+        if not self.cfg.overlap:
+            self._backward(self.B)
+            self._update(peers=True)
+            return
+        # Two buckets in gradient-ready order (SURVEY 5.5 "Overlap"): the fc bucket (98% of the
+        # bytes) closes first and its fused allreduce+update runs on the comm stream underneath the
+        # convolution backward; the small conv bucket follows on the main stream.
+        main = torch.cuda.current_stream()
+        split = self.spec.param("fc1_weight").offset
+        self._backward_fc(self.B)
+        self._ev_fc.record(main)
+        self._comm_stream.wait_event(self._ev_fc)
+        with torch.cuda.stream(self._comm_stream):
+            self._update(peers=True, lo=split, hi=self.n, advance=False)
+            self._ev_done.record(self._comm_stream)
+        self._backward_conv(self.B)
+        main.wait_event(self._ev_done)
+        self._update(peers=True, lo=0, hi=split, advance=True)
 
     def fused_step(self, images, labels, lr, step: int, read_loss: bool = True):
         """One full step: (window | staged batch) -> graph replay.  ``lr`` is ignored: the

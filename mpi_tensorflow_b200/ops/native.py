@@ -31,6 +31,7 @@ class FusedArgs(C.Structure):
         ("momentum", f32), ("beta1", f32), ("beta2", f32), ("eps", f32), ("wd", f32),
         ("n_ranges", i32), ("range_begin", i64 * 8), ("range_end", i64 * 8),
         ("grid", i32), ("block", i32),
+        ("advance_step", vp), ("done_counter", vp),
     ]
 
 
@@ -46,6 +47,7 @@ _SIGS = {
                       vp, vp, vp],
     "mtb_init_trunc_normal": [vp, i64, f32, u64, C.c_uint, vp],
     "mtb_fill_f32": [vp, i64, f32, vp],
+    "mtb_zero_multi": [vp, vp, i32, vp],
     "mtb_normalize_u8_dev": [vp, vp, i64, vp],
     "mtb_synthetic_batch": [vp, vp, i64, i64, u64, i32, vp],
     "mtb_batch_window": [vp, vp, vp, i64, i32, vp, vp, vp],
@@ -61,6 +63,8 @@ _SIGS = {
     "mtb_im2col_5x5": [vp, vp, i32, i32, i32, i32, vp],
     "mtb_col2im_5x5": [vp, vp, i32, i32, i32, i32, vp],
     "mtb_fc2_softmax_ce": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "mtb_fc2_softmax_ce_fast": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "mtb_fc2_bwd_fused": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, vp],
     "mtb_fc2_dgrad": [vp, vp, vp, vp, i32, i32, i32, f32, vp],
     "mtb_fc2_wgrad": [vp, vp, vp, vp, i32, i32, i32, vp],
     "mtb_colsum_bf16": [vp, vp, i64, i32, vp],

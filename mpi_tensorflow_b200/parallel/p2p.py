@@ -52,7 +52,8 @@ class P2PComm(Communicator):
         self._allocs: List[Tuple[int, List[int]]] = []
         flag_bytes = self._L.mtb_fused_flag_bytes()
         # control block: [flags | seq (1 KiB) | status (256 B)]
-        self.ctrl = self.alloc_symmetric(flag_bytes + 1024 + 256)
+        self._seq_bytes = 4 * self._L.mtb_fused_max_blocks()
+        self.ctrl = self.alloc_symmetric(flag_bytes + self._seq_bytes + 256)
         self._flag_bytes = flag_bytes
         self.staging = self.alloc_symmetric(staging_bytes)
         self.staging_bytes = staging_bytes
@@ -87,13 +88,14 @@ class P2PComm(Communicator):
         for r in range(self.size):
             a.flags[r] = self.ctrl.ptrs[r]
         a.seq = self.ctrl.local_ptr + self._flag_bytes
-        a.status = self.ctrl.local_ptr + self._flag_bytes + 1024
+        a.status = self.ctrl.local_ptr + self._flag_bytes + self._seq_bytes
         a.lr_override = -1.0
         a.scale = 1.0
         return a
 
     def check_status(self) -> None:
-        st = self.ctrl.local[self._flag_bytes + 1024:self._flag_bytes + 1028].view(torch.int32)
+        o = self._flag_bytes + self._seq_bytes
+        st = self.ctrl.local[o:o + 4].view(torch.int32)
         code = int(st.item())
         if code != 0:
             st.zero_()

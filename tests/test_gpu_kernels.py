@@ -223,6 +223,23 @@ def test_fc2_softmax_ce_fwd_bwd(N, dev, B, F):
     assert _rel(dW.cpu(), h.cpu().float().t() @ rdl) < 1e-4
     assert _rel(db.cpu(), rdl.sum(0)) < 1e-4
     assert _rel(cs.cpu(), dh.cpu().float().sum(0)) < 1e-4
+    # engine variants: same math, shared-memory weights / one fused backward pass
+    l2, p2, d2 = (torch.zeros(B, NC, device=dev) for _ in range(3))
+    loss2 = torch.zeros(1, device=dev)
+    err2 = torch.zeros(1, dtype=torch.int32, device=dev)
+    N.call("mtb_fc2_softmax_ce_fast", h.data_ptr(), W.data_ptr(), bias.data_ptr(), y.data_ptr(), l2.data_ptr(),
+           p2.data_ptr(), d2.data_ptr(), loss2.data_ptr(), err2.data_ptr(), B, F, NC)
+    dh2 = torch.zeros(B, F, dtype=torch.bfloat16, device=dev)
+    dW2, db2, db1 = torch.zeros(F, NC, device=dev), torch.zeros(NC, device=dev), torch.zeros(F, device=dev)
+    N.call("mtb_fc2_bwd_fused", h.data_ptr(), dl.data_ptr(), W.data_ptr(), dh2.data_ptr(), dW2.data_ptr(),
+           db2.data_ptr(), db1.data_ptr(), B, F, NC, 2.0)
+    torch.cuda.synchronize()
+    assert torch.allclose(l2, logits, atol=1e-4, rtol=1e-4) and torch.allclose(d2, dl, atol=1e-7, rtol=1e-3)
+    assert abs(float(loss2) - float(loss)) < 1e-4 and int(err2) == int(err)
+    assert _rel(dh2.cpu(), rdh) < 5e-3
+    assert _rel(dW2.cpu(), h.cpu().float().t() @ rdl) < 1e-4
+    assert _rel(db2.cpu(), rdl.sum(0)) < 1e-4
+    assert _rel(db1.cpu(), dh2.cpu().float().sum(0)) < 1e-4
 
 
 # ----------------------------------------------------------------------------- init / data / misc
@@ -291,7 +308,7 @@ def test_fused_update_single_gpu_matches_oracle(N, dev, opt):
     W, G = w.clone().to(dev), g.clone().to(dev)
     M, V = m0.clone().to(dev), v0.clone().to(dev)
     S = torch.zeros(n, dtype=torch.bfloat16, device=dev)
-    seq = torch.zeros(256, dtype=torch.int32, device=dev)
+    seq = torch.zeros(512, dtype=torch.int32, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     st = torch.tensor([step], dtype=torch.int64, device=dev)
     a = N.FusedArgs()
