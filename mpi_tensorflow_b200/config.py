@@ -49,7 +49,8 @@ class TrainConfig:
     comm_dtype: str = "fp32"            # gradient wire format: fp32 | bf16
     backend: str = "auto"               # auto | p2p | nccl | gloo | shm | self
     device: str = "auto"                # auto | cuda | cpu
-    overlap: bool = True                # bucketed comm overlapped with backward
+    overlap: bool = False               # fc-bucket allreduce+update on a comm stream under the conv backward
+                                        # (measured slower than the single launch on 2 and 8 B200s: off)
     # eval / logging
     eval_every: int = 50                # reference: 1 (mpipy.py:86)
     eval_dropout: bool = False          # reference: True (mpipy.py:166 via :68)

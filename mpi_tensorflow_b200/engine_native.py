@@ -60,7 +60,7 @@ class NativeEngine:
         self.rows = 0
         self.decay_rows = cfg.lr_decay_rows
         self._side = torch.cuda.Stream(device=device)
-        self._comm_stream = torch.cuda.Stream(device=device)
+        self._comm_stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("MTB_COMM_PRIO", "-1")))
         self._ev_fc, self._ev_done = torch.cuda.Event(), torch.cuda.Event()
         self.last_aux: Dict = {}
 
@@ -348,12 +348,13 @@ class NativeEngine:
         return 1 if count * 4 > (256 << 10) else 0
 
     def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
-                advance: bool = True):
+                advance: bool = True, grid: int = 0):
         """K1 over elements [lo, hi) of the flat buffers; ``advance`` also bumps the step counter."""
         hi = self.n if hi is None else hi
         a = self._fused_args(peers, lr_override)
         a.offset, a.count = lo, hi - lo
         a.algo = self._pick_algo(hi - lo) if peers else 0
+        a.grid = grid
         if advance:                                                     # iter_ += 1 in the same launch
             a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done.data_ptr()
         N.call("mtb_fused_allreduce_update", C.byref(a))
@@ -406,7 +407,8 @@ class NativeEngine:
         self._ev_fc.record(main)
         self._comm_stream.wait_event(self._ev_fc)
         with torch.cuda.stream(self._comm_stream):
-            self._update(peers=True, lo=split, hi=self.n, advance=False)
+            self._update(peers=True, lo=split, hi=self.n, advance=False,
+                         grid=int(os.environ.get("MTB_K1_GRID_A", "148")))
             self._ev_done.record(self._comm_stream)
         self._backward_conv(self.B)
         main.wait_event(self._ev_done)
