@@ -353,3 +353,112 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Split-K GEMM for callers that cannot hand us scratch memory.
+//
+// The split-K path above needs a workspace for the per-split partial tiles and a counter per
+// output tile, both supplied by the caller.  Some users of this C ABI have no way to supply
+// them: a plug-in loaded into a host process whose own allocator has already reserved the
+// whole GPU (a raw cudaMalloc from the plug-in fails or steals from the host's budget), a
+// control loop that must not call the allocator once it is running because cudaMalloc
+// synchronises the device, or a small C program that links this library alone and has no
+// tensor library to allocate with.  For them the scratch lives in the library image itself: a
+// fixed array in device global memory, one copy on every GPU that loads libmtb200.so, held
+// until the process exits.
+namespace {
+
+constexpr size_t kNoAllocWorkspaceBytes = 4u << 20;      // partial tiles: tiles * splits * 128 * bn * 4 bytes
+constexpr size_t kNoAllocCounterBytes = 4u << 10;        // one 32-bit counter per output tile
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocWorkspaceBytes + kNoAllocCounterBytes];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address, so
+// the address is looked up once per device (with that device current) and remembered.
+void* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+
+int noalloc_scratch(void** out) {
+  int dev = -1;
+  MTB_CUDA_CHECK(cudaGetDevice(&dev));
+  MTB_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "gemm_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    MTB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t mtb_gemm_noalloc_max_workspace_bytes(void) { return kNoAllocWorkspaceBytes; }
+
+// Same product and epilogue (bias, ReLU, bf16 or fp32 output) as mtb_gemm_bf16 with split-K,
+// but with no workspace / counter arguments and no allocation of any kind: no cudaMalloc, no
+// cudaFree, no tensor-library call.  Limits: the partial tiles (see
+// mtb_gemm_workspace_bytes) must fit in 4 MiB and the tile counters in 4 KiB; larger
+// problems are refused with MTB_E_LIMIT.
+//
+// The first call on each device looks up the scratch array's device address.  Make that first
+// call during start-up, before any stream capture is begun on that device.
+//
+// Every call on a device uses the same array and finds whatever the previous call left in it.
+// The tile counters have to start at zero, so each call clears them on `stream` before the
+// kernel; the partial tiles are fully overwritten before they are read.  Two calls that can
+// execute at the same time on one GPU (different streams, or different host threads) would
+// share the array and corrupt each other: callers must serialise them.
+int mtb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major,
+                                 int b_mn_major, long long lda, long long ldb, long long ldc, int out_bf16,
+                                 const float* bias, int relu, int bn, int splits, cudaStream_t stream) {
+  MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm_noalloc: null pointer or empty shape");
+  MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm_noalloc: operand row pitch must be a multiple of 16 bytes");
+  MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_noalloc: operands must be 16-byte aligned");
+  if (bn != 64 && bn != 128) bn = 64;
+  if (splits < 1) splits = 1;
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_total = (int)mtb::ceil_div(K, BK);
+  if (splits > p.kb_total) splits = p.kb_total;
+  p.kb_per_split = (int)mtb::ceil_div(p.kb_total, splits);
+  splits = (int)mtb::ceil_div(p.kb_total, p.kb_per_split);
+  p.splits = splits;
+  const size_t tiles = (size_t)mtb::ceil_div(M, BM) * (size_t)mtb::ceil_div(N, bn);
+  const size_t ws_bytes = splits > 1 ? tiles * (size_t)splits * BM * bn * sizeof(float) : 0;
+  const size_t cnt_bytes = tiles * sizeof(unsigned int);
+  if (ws_bytes > kNoAllocWorkspaceBytes || cnt_bytes > kNoAllocCounterBytes)
+    return mtb_set_error_msg(MTB_E_LIMIT,
+                             "gemm_noalloc: split-K scratch for this shape exceeds the built-in 4 MiB + 4 KiB array; "
+                             "use mtb_gemm_bf16 with caller-provided workspace", __FILE__, __LINE__);
+  void* scratch = nullptr;
+  if (int e = noalloc_scratch(&scratch)) return e;
+  unsigned char* base = reinterpret_cast<unsigned char*>(scratch);
+  p.workspace = reinterpret_cast<float*>(base);
+  p.counters = reinterpret_cast<unsigned int*>(base + kNoAllocWorkspaceBytes);
+  MTB_CUDA_CHECK(cudaMemsetAsync(p.counters, 0, cnt_bytes, stream));
+  p.out = out; p.ldc = ldc; p.out_bf16 = out_bf16; p.bias = bias; p.relu = relu;
+  p.keep_prob = 1.0f; p.seed = 0; p.step_ptr = nullptr;
+  // tensor maps are encoded on the stack here: the cached path of mtb_gemm_bf16 would grow a host map
+  CUtensorMap ma, mb;
+  bool ok;
+  ok = a_mn_major ? tma::make_2d_sw128(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, 64, 64)
+                  : tma::make_2d_sw128(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, BM, 64);
+  MTB_REQUIRE(ok, "gemm_noalloc: cuTensorMapEncodeTiled failed for A");
+  ok = b_mn_major ? tma::make_2d_sw128(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64, 64)
+                  : tma::make_2d_sw128(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, (uint32_t)bn, 64);
+  MTB_REQUIRE(ok, "gemm_noalloc: cuTensorMapEncodeTiled failed for B");
+#define MTB_GEMM_CASE(BN_, AM_, BM_)                                            \
+  if (bn == BN_ && (a_mn_major != 0) == AM_ && (b_mn_major != 0) == BM_) return launch<BN_, AM_, BM_>(ma, mb, p, stream);
+  MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)
+  MTB_GEMM_CASE(128, true, true) MTB_GEMM_CASE(64, false, false) MTB_GEMM_CASE(64, false, true)
+  MTB_GEMM_CASE(64, true, false) MTB_GEMM_CASE(64, true, true)
+#undef MTB_GEMM_CASE
+  return mtb_set_error_msg(MTB_E_ARG, "gemm_noalloc: no kernel variant", __FILE__, __LINE__);
+}
+
+}  // extern "C"

@@ -48,6 +48,18 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
                   float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
                   void* workspace, void* counters, cudaStream_t stream);
 
+/* Split-K GEMM with built-in scratch, for callers that cannot allocate or pass device scratch (a plug-in inside a
+ * process whose allocator owns the whole GPU, an allocation-free control loop, a bare C caller without a tensor
+ * library).  No counterpart in the reference.  Same product/epilogue as mtb_gemm_bf16 (bias, ReLU, bf16/fp32
+ * output; no dropout).  Scratch is a fixed 4 MiB + 4 KiB device array inside the library, one per GPU, kept until
+ * exit; shapes whose split-K partials need more return MTB_E_LIMIT.  Allocates nothing.  First call per device
+ * resolves the array's address: do it at start-up, before any stream capture.  Calls share the array: never let two
+ * of them overlap on one GPU. */
+size_t mtb_gemm_noalloc_max_workspace_bytes(void);
+int mtb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major,
+                                 int b_mn_major, long long lda, long long ldb, long long ldc, int out_bf16,
+                                 const float* bias, int relu, int bn, int splits, cudaStream_t stream);
+
 /* ---- init / data / casts (tf.truncated_normal mpipy.py:38-52; extract_data mpipy.py:215) ---- */
 int mtb_init_trunc_normal(float* dst, long long n, float stddev, unsigned long long seed, unsigned stream_id,
                           cudaStream_t stream);
