@@ -56,6 +56,7 @@ class NativeEngine:
         self.opt_step = 0
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_key = None
+        self._stream_state = None
         self.data_x = self.data_y = None
         self.rows = 0
         self.decay_rows = cfg.lr_decay_rows
@@ -429,6 +430,71 @@ class NativeEngine:
             self._step_body()
         self.opt_step += 1
         return float(self.loss_acc.item()) if read_loss else 0.0
+
+    # ------------------------------------------------------------------ host-streamed training
+    def stream_steps(self, hx: torch.Tensor, hy: torch.Tensor, steps: int, ring: int = 4) -> List[float]:
+        """``steps`` optimizer steps over a dataset that lives in PINNED HOST memory
+        (``hx`` [rows, 784] fp32, ``hy`` [rows] int32), walked with the reference's sequential
+        window (``mpipy.py:80-82``).  This is the reference's feed loop (``mpipy.py:83-85``: one
+        host->device feed per step) done the B200 way: step i+1's batch is copied on a copy
+        stream into the other half of a double buffer while step i computes, and each step's
+        loss is copied back to a pinned ring that the host reads a few steps later, so neither
+        transfer ever stalls the GPU.  Returns the loss of every step."""
+        B, dev = self.B, self.device
+        if not (hx.is_pinned() and hy.is_pinned()):
+            raise ValueError("stream_steps needs pinned host tensors (tensor.pin_memory())")
+        if hy.dtype != torch.int32 or hx.dtype != torch.float32:
+            raise ValueError("stream_steps needs float32 images and int32 labels")
+        hx = hx.view(hx.shape[0], -1)
+        nwin = hx.shape[0] // B
+        if nwin < 1:
+            raise ValueError("dataset smaller than one batch")
+        if self._stream_state is None:
+            self._stream_state = dict(
+                x=[torch.empty(B, 784, device=dev) for _ in range(2)],
+                y=[torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)],
+                ready=[torch.cuda.Event() for _ in range(2)],
+                consumed=[torch.cuda.Event() for _ in range(2)],
+                copy=torch.cuda.Stream(device=dev),
+                loss=torch.zeros(ring, dtype=torch.float32).pin_memory(),
+                loss_ev=[torch.cuda.Event() for _ in range(ring)],
+            )
+        st = self._stream_state
+        ring = st["loss"].numel()
+        main = torch.cuda.current_stream()
+        copy = st["copy"]
+        for ev in st["consumed"]:
+            ev.record(main)
+        if self.cfg.cuda_graph and self._graph is None:
+            self._capture()
+        losses: List[float] = []
+        for i in range(steps):
+            k, r = i & 1, i % ring
+            o = (i % nwin) * B
+            copy.wait_event(st["consumed"][k])                 # the step that used this half has copied it out
+            with torch.cuda.stream(copy):
+                st["x"][k].copy_(hx[o:o + B], non_blocking=True)
+                st["y"][k].copy_(hy[o:o + B], non_blocking=True)
+                st["ready"][k].record(copy)
+            main.wait_event(st["ready"][k])
+            self.x_in[:B].copy_(st["x"][k], non_blocking=True)
+            self.y_in[:B].copy_(st["y"][k], non_blocking=True)
+            st["consumed"][k].record(main)
+            if self.cfg.cuda_graph:
+                self._graph.replay()
+            else:
+                self._step_body()
+            if i >= ring:                                      # oldest slot of the ring: read it before reuse
+                st["loss_ev"][r].synchronize()
+                losses.append(float(st["loss"][r]))
+            st["loss"][r:r + 1].copy_(self.loss_acc, non_blocking=True)
+            st["loss_ev"][r].record(main)
+            self.opt_step += 1
+        for i in range(max(0, steps - ring), steps):
+            r = i % ring
+            st["loss_ev"][r].synchronize()
+            losses.append(float(st["loss"][r]))
+        return losses
 
     def _capture(self):
         """Warm up eagerly (sets kernel attributes, builds tensor maps), roll the state back, capture."""

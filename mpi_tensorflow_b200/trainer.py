@@ -146,6 +146,30 @@ class Trainer:
         self.global_step += 1
         return float(loss)
 
+    def fit_stream(self, images, labels, steps: int):
+        """Train ``steps`` steps from a dataset kept in host memory, one host->device batch copy
+        and one device->host loss read per step (the reference's feed loop, ``mpipy.py:79-85``),
+        with copies overlapped with compute on the GPU engine.  ``images`` [rows,28,28,1] or
+        [rows,784] float32, ``labels`` [rows] integer; they are pinned here if they are not
+        already.  Returns the list of per-step losses."""
+        x = torch.as_tensor(images, dtype=torch.float32)
+        y = torch.as_tensor(labels).to(torch.int32)
+        if not self._fused or not hasattr(self.engine, "stream_steps"):
+            B, rows = self.cfg.batch, x.shape[0]
+            out = []
+            for i in range(steps):
+                o = (i % (rows // B)) * B
+                out.append(self.step(x[o:o + B], y[o:o + B]))
+            return out
+        x = x if x.is_pinned() else x.pin_memory()
+        y = y if y.is_pinned() else y.pin_memory()
+        if not self.decay_rows:
+            self.decay_rows = x.shape[0]
+            self.engine.decay_rows = self.engine.decay_rows or x.shape[0]
+        losses = self.engine.stream_steps(x, y, steps)
+        self.global_step += steps
+        return losses
+
     # ------------------------------------------------------------------ eval
     def eval_in_batches(self, data, dropout_step: Optional[int] = None) -> np.ndarray:
         """Softmax predictions ``[size, classes]`` in fixed batches; the ragged tail
