@@ -56,7 +56,8 @@ def parse():
     ap.add_argument("--comm-algo", default="auto")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--overlap", action="store_true", help="fc-bucket K1 on a comm stream under the conv backward")
+    ap.add_argument("--no-overlap", action="store_true", help="(default) one K1 launch at the end of the step")
     ap.add_argument("--dtype", default="bf16")
     return ap.parse_args()
 
@@ -171,7 +172,7 @@ def run_ours(args) -> dict:
     B, K, W = args.batch, args.steps, args.warmup
     cfg = TrainConfig(model=args.model, batch=B, dtype=args.dtype, optimizer=args.optimizer, eval_every=0,
                       log_every=0, dropout=True, cuda_graph=not args.no_graph, comm_algo=args.comm_algo,
-                      overlap=not args.no_overlap,
+                      overlap=args.overlap and not args.no_overlap,
                       lr=0.01 if args.optimizer != "adam" else 1e-4)
     tr = Trainer(cfg, comm)
     eng = tr.engine

@@ -95,9 +95,12 @@ __device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* p, uint2 v) {
   asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
-// All ranks' block `b` meet here.  Every thread fences its own prior stores first.
-__device__ void cross_gpu_barrier(const FusedParams& p, int b, uint32_t val) {
-  __threadfence_system();
+// All ranks' block `b` meet here.  With `fence`, every thread first makes its own stores (to
+// peer memory) visible system-wide; without, the barrier only orders control flow, which is
+// all the opening round needs: the gradients it guards were written by earlier kernels, and a
+// kernel boundary already made them visible to peer loads.
+__device__ void cross_gpu_barrier(const FusedParams& p, int b, uint32_t val, bool fence) {
+  if (fence) __threadfence_system();
   __syncthreads();
   if ((int)threadIdx.x < p.world) {
     const int peer = threadIdx.x;
@@ -187,7 +190,7 @@ fused_allreduce_update_kernel(const FusedParams p) {
   const uint32_t seq = s_seq;
   const Hyper h = make_hyper(p);
   const bool multi = p.world > 1;
-  if (multi) cross_gpu_barrier(p, b, seq + 1);       // every peer's gradients are complete
+  if (multi) cross_gpu_barrier(p, b, seq + 1, false);   // every peer's gradients are complete
 
   const long long vec_total = p.count >> 2;
   if (!multi || p.algo == 0) {
@@ -242,7 +245,9 @@ fused_allreduce_update_kernel(const FusedParams p) {
       }
     }
   }
-  if (multi) cross_gpu_barrier(p, b, seq + 2);       // peers are done reading my grads / writing my params
+  // peers are done reading my grads (loads have retired: their values were consumed) and, in the
+  // two-shot / nvls forms, done writing my params (needs the fence)
+  if (multi) cross_gpu_barrier(p, b, seq + 2, p.algo != 0);
   if (threadIdx.x == 0) {
     p.seq[b] = seq + 2;
     if (p.advance_step != nullptr) {
@@ -261,7 +266,7 @@ __global__ void barrier_kernel(const FusedParams p) {
   if (threadIdx.x == 0) s_seq = p.seq[0];
   __syncthreads();
   const uint32_t seq = s_seq;
-  cross_gpu_barrier(p, 0, seq + 2);
+  cross_gpu_barrier(p, 0, seq + 2, true);
   if (threadIdx.x == 0) p.seq[0] = seq + 2;
 }
 
@@ -318,7 +323,8 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   long long vecs = p.count >> 2;
   if (p.world > 1 && p.algo != 0) vecs = (vecs + p.world - 1) / p.world;
   int grid = a->grid > 0 ? a->grid : 3 * 148;
-  long long need = (vecs + block - 1) / block;
+  // at least 4 vectors (64 bytes) per thread before another block (and its flag round) pays off
+  long long need = (vecs + 4 * block - 1) / (4 * block);
   if (need < 1) need = 1;
   if (grid > need) grid = (int)need;
   if (grid > kMaxBlocks) grid = kMaxBlocks;
