@@ -70,11 +70,14 @@ def main():
         elems = size // 4
         iters = 200 if size <= (1 << 20) else (50 if size <= (64 << 20) else 10)
         rec = {"bytes": size, "n_gpus": n}
-        for name, algo in (("p2p_oneshot", 0), ("p2p_twoshot", 1)):
+        variants = [("p2p_oneshot", 0), ("p2p_twoshot", 1)] + ([("p2p_nvls", 2)] if src.mc_ptr and dst.mc_ptr else [])
+        for name, algo in variants:
             if algo == 0 and size > (64 << 20):
                 continue
             args = comm.fused_args()
             args.algo, args.optimizer = algo, -1
+            if algo == 2:
+                args.mc_grads, args.mc_params = src.mc_ptr, dst.mc_ptr
             for k in range(n):
                 args.grads[k] = src.ptrs[k]
                 args.params[k] = dst.ptrs[k]

@@ -70,18 +70,21 @@ class NativeEngine:
         """Symmetric (peer-mapped) allocation under p2p, plain device memory otherwise."""
         if self.p2p is not None:
             sb = self.p2p.alloc_symmetric(nbytes)
-            return sb.local, sb.ptrs
+            self._sym_keep.append(sb)
+            return sb.local, sb.ptrs, sb.mc_ptr
         t = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
-        return t, [t.data_ptr()]
+        return t, [t.data_ptr()], 0
 
     def _alloc_state(self):
         n, dev = self.n, self.device
-        raw, self._param_ptrs = self._sym(n * 4)
-        self.flat_params = raw.view(torch.float32)
-        raw, self._grad_ptrs = self._sym(n * 4)
-        self.flat_grads = raw.view(torch.float32)
-        raw, self._shadow_ptrs = self._sym(n * 2)
-        self.shadow = raw.view(torch.bfloat16)
+        self._sym_keep = []
+        raw, self._param_ptrs, self._param_mc = self._sym(n * 4)
+        self.flat_params = raw[:n * 4].view(torch.float32)
+        raw, self._grad_ptrs, self._grad_mc = self._sym(n * 4)
+        self.flat_grads = raw[:n * 4].view(torch.float32)
+        raw, self._shadow_ptrs, self._shadow_mc = self._sym(n * 2)
+        self.shadow = raw[:n * 2].view(torch.bfloat16)
+        self.has_nvls = bool(self._param_mc and self._grad_mc and self._shadow_mc)
         self.slots: List[torch.Tensor] = []
         if self.cfg.optimizer in ("momentum", "adam"):
             self.slots.append(torch.zeros(n, device=dev))
@@ -319,6 +322,8 @@ class NativeEngine:
             a = self.p2p.fused_args()
             for r in range(self.world):
                 a.grads[r], a.params[r], a.shadow[r] = self._grad_ptrs[r], self._param_ptrs[r], self._shadow_ptrs[r]
+            if self.has_nvls:
+                a.mc_grads, a.mc_params, a.mc_shadow = self._grad_mc, self._param_mc, self._shadow_mc
             a.scale = 1.0 / self.world
         else:
             a = N.FusedArgs()
@@ -346,7 +351,13 @@ class NativeEngine:
             return 0
         if algo == "twoshot":
             return 1
-        return 1 if count * 4 > (256 << 10) else 0
+        if algo == "nvls":
+            if not self.has_nvls:
+                raise RuntimeError("comm_algo='nvls' but no multicast mapping is available on this box")
+            return 2
+        if count * 4 <= (256 << 10):
+            return 0
+        return 2 if self.has_nvls else 1
 
     def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
                 advance: bool = True, grid: int = 0):

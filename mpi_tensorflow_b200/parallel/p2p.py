@@ -15,9 +15,11 @@ straight to ``mtb_fused_allreduce_update``.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Tuple
 
 import torch
+import torch.distributed
 
 from ..ops import native as N
 from .comm import CommTimeout, Communicator, TorchComm
@@ -26,10 +28,13 @@ from .comm import CommTimeout, Communicator, TorchComm
 class SymmetricBuffer:
     """One allocation per rank, same size everywhere, all of them mapped locally."""
 
-    def __init__(self, local_ptr: int, peer_ptrs: List[int], nbytes: int, rank: int, device: torch.device):
+    def __init__(self, local_ptr: int, peer_ptrs: List[int], nbytes: int, rank: int, device: torch.device,
+                 mc_ptr: int = 0, local: Optional[torch.Tensor] = None, keep=None):
         self.ptrs, self.nbytes, self.rank, self.device = peer_ptrs, nbytes, rank, device
         self.local_ptr = local_ptr
-        self.local = N.tensor_from_ptr(local_ptr, nbytes, device)
+        self.mc_ptr = mc_ptr                      # NVLS multicast address of the same bytes on every rank (0: none)
+        self.local = local if local is not None else N.tensor_from_ptr(local_ptr, nbytes, device)
+        self._keep = keep                         # whatever owns the mapping
 
     def view(self, rank: int) -> torch.Tensor:
         """uint8 view of ``rank``'s copy (peer memory mapped into this process)."""
@@ -49,6 +54,25 @@ class P2PComm(Communicator):
         torch.cuda.set_device(device)
         self.boot = boot if boot is not None else (TorchComm("gloo", timeout_s) if self.size > 1 else None)
         self._L = N.lib()
+        # Allocator: torch's symmetric memory (CUDA VMM handles; also binds an NVLS multicast
+        # object when the fabric has one) if it works here, else plain CUDA-IPC arenas.
+        self.allocator = os.environ.get("MTB_P2P_ALLOC", "auto")       # auto | symm | ipc
+        self._symm = None
+        if self.size > 1 and self.allocator in ("auto", "symm") and isinstance(self.boot, TorchComm):
+            try:
+                import torch.distributed._symmetric_memory as symm
+                probe = symm.empty(256, dtype=torch.uint8, device=device)
+                symm.rendezvous(probe, group=torch.distributed.group.WORLD)
+                self._symm = symm
+            except Exception as e:  # noqa: BLE001
+                if self.allocator == "symm":
+                    raise
+                self._symm = None
+            # every rank must take the same path
+            oks = self.boot.allgather_object(self._symm is not None)
+            if not all(oks):
+                self._symm = None
+        self.has_multicast = False
         self._allocs: List[Tuple[int, List[int]]] = []
         flag_bytes = self._L.mtb_fused_flag_bytes()
         # control block: [flags | seq (1 KiB) | status (256 B)]
@@ -62,6 +86,17 @@ class P2PComm(Communicator):
     # ------------------------------------------------------------------ memory
     def alloc_symmetric(self, nbytes: int) -> SymmetricBuffer:
         nbytes = (nbytes + 255) // 256 * 256
+        if self._symm is not None:
+            t = self._symm.empty(nbytes, dtype=torch.uint8, device=self.device)
+            t.zero_()
+            h = self._symm.rendezvous(t, group=torch.distributed.group.WORLD)
+            ptrs = [int(p) for p in h.buffer_ptrs]
+            mc = int(getattr(h, "multicast_ptr", 0) or 0)
+            self.has_multicast = self.has_multicast or mc != 0
+            torch.cuda.current_stream().synchronize()
+            self._allocs.append((0, []))
+            return SymmetricBuffer(ptrs[self.rank], ptrs, nbytes, self.rank, self.device, mc_ptr=mc, local=t,
+                                   keep=(t, h))
         p = C.c_void_p()
         N.check(self._L.mtb_arena_alloc(nbytes, C.byref(p)), "arena_alloc")
         ptrs = [0] * self.size
@@ -234,7 +269,8 @@ class P2PComm(Communicator):
                 if r != self.rank and q:
                     self._L.mtb_ipc_close(C.c_void_p(q))
         for local, _ in self._allocs:
-            self._L.mtb_arena_free(C.c_void_p(local))
+            if local:
+                self._L.mtb_arena_free(C.c_void_p(local))
         self._allocs.clear()
         if self.boot is not None:
             self.boot.close()

@@ -63,9 +63,11 @@ def fused(comm, outdir):
     r, n, dev = comm.rank, comm.size, comm.device
     b, steps = 32, 6
     finals = {}
-    for algo in ("oneshot", "twoshot"):
+    algos = ["oneshot", "twoshot"] + (["nvls"] if getattr(comm, "has_multicast", False) else [])
+    print(f"rank {r}: allocator={'symm' if comm._symm is not None else 'ipc'} multicast={comm.has_multicast}", flush=True)
+    for algo in algos:
         cfg = TrainConfig(model="tutorial512", batch=b, eval_every=0, log_every=0, dropout=False,
-                          comm_algo=algo, cuda_graph=(algo == "twoshot"), lr_decay_rows=10 ** 9)
+                          comm_algo=algo, cuda_graph=(algo != "oneshot"), lr_decay_rows=10 ** 9)
         tr = Trainer(cfg, comm)
         # rank r trains on rows [r*b, (r+1)*b) of every global batch of n*b rows
         rows = steps * b + b
@@ -100,8 +102,9 @@ def fused(comm, outdir):
             t1.close()
         tr.close()
         comm.barrier()
-    rel = float((finals["oneshot"] - finals["twoshot"]).norm() / finals["oneshot"].norm())
-    assert rel < 1e-3, f"oneshot vs twoshot: {rel}"
+    for algo in algos[1:]:
+        rel = float((finals["oneshot"] - finals[algo]).norm() / finals["oneshot"].norm())
+        assert rel < 1e-3, f"oneshot vs {algo}: {rel}"
     print(f"GPU_FUSED_OK rank {r}/{n}", flush=True)
 
 
