@@ -180,6 +180,60 @@ __device__ __forceinline__ uint2 to_bf16x4(float4 w) {
   return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
 }
 
+enum Kind { kLocal = 0, kOneShot = 1, kTwoShot = 2, kNvls = 3 };
+
+// Vectors [lo, hi) of the bucket, kUnroll per thread per pass: all reductions (peer loads or
+// switch-reduced multimem loads) of a pass are issued before any of them is used, which is what
+// keeps enough bytes in flight to cover NVLink latency.
+template <int KIND>
+__device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, long long lo, long long hi) {
+  constexpr int kUnroll = 4;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long v0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * kUnroll) {
+    float4 g[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = v0 + u * stride;
+      g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (v < hi) {
+        const long long i = p.offset + (v << 2);
+        if (KIND == kLocal) {
+          g[u] = *reinterpret_cast<const float4*>(p.grads[0] + i);
+        } else if (KIND == kNvls) {
+          g[u] = multimem_ld_reduce_f4(p.mc_grads + i);
+        } else {
+          for (int r = 0; r < p.world; ++r) {       // rank order: every replica sums identically
+            const float4 t = ld_peer_f4(p.grads[r] + i);
+            g[u].x += t.x; g[u].y += t.y; g[u].z += t.z; g[u].w += t.w;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = v0 + u * stride;
+      if (v >= hi) continue;
+      const long long i = p.offset + (v << 2);
+      float4 gs = g[u];
+      gs.x *= p.scale; gs.y *= p.scale; gs.z *= p.scale; gs.w *= p.scale;
+      const float4 w = apply_update(p, h, i, gs);
+      const uint2 wb = to_bf16x4(w);
+      if (KIND == kLocal || KIND == kOneShot) {
+        *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
+        if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = wb;
+      } else if (KIND == kNvls) {
+        multimem_st_f4(p.mc_params + i, w);
+        if (p.mc_shadow) multimem_st_bf16x4(p.mc_shadow + i, wb);
+      } else {
+        for (int r = 0; r < p.world; ++r) {
+          *reinterpret_cast<float4*>(p.params[r] + i) = w;
+          if (p.shadow[r]) *reinterpret_cast<uint2*>(p.shadow[r] + i) = wb;
+        }
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 fused_allreduce_update_kernel(const FusedParams p) {
   const int b = blockIdx.x;
@@ -193,57 +247,17 @@ fused_allreduce_update_kernel(const FusedParams p) {
   if (multi) cross_gpu_barrier(p, b, seq + 1, false);   // every peer's gradients are complete
 
   const long long vec_total = p.count >> 2;
-  if (!multi || p.algo == 0) {
-    // ---- one-shot (and the single-GPU fused optimizer) ----
-    for (long long v = (long long)b * blockDim.x + threadIdx.x; v < vec_total; v += (long long)gridDim.x * blockDim.x) {
-      const long long i = p.offset + (v << 2);
-      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (!multi) {
-        g = *reinterpret_cast<const float4*>(p.grads[0] + i);
-      } else {
-#pragma unroll 4
-        for (int r = 0; r < p.world; ++r) {
-          const float4 t = ld_peer_f4(p.grads[r] + i);
-          g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
-        }
-      }
-      g.x *= p.scale; g.y *= p.scale; g.z *= p.scale; g.w *= p.scale;
-      const float4 w = apply_update(p, h, i, g);
-      *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
-      if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = to_bf16x4(w);
-    }
+  if (!multi) {
+    run_range<kLocal>(p, h, 0, vec_total);
+  } else if (p.algo == 0) {
+    run_range<kOneShot>(p, h, 0, vec_total);
   } else {
-    // ---- two-shot / nvls: this rank owns one contiguous slice ----
+    // two-shot / nvls: this rank owns one contiguous slice
     const long long per = (vec_total + p.world - 1) / p.world;
     const long long lo = per * p.rank < vec_total ? per * p.rank : vec_total;
     const long long hi = lo + per < vec_total ? lo + per : vec_total;
-    for (long long v = lo + (long long)b * blockDim.x + threadIdx.x; v < hi; v += (long long)gridDim.x * blockDim.x) {
-      const long long i = p.offset + (v << 2);
-      float4 g;
-      if (p.algo == 2) {
-        g = multimem_ld_reduce_f4(p.mc_grads + i);
-      } else {
-        g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-        for (int r = 0; r < p.world; ++r) {
-          const float4 t = ld_peer_f4(p.grads[r] + i);
-          g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
-        }
-      }
-      g.x *= p.scale; g.y *= p.scale; g.z *= p.scale; g.w *= p.scale;
-      const float4 w = apply_update(p, h, i, g);
-      const uint2 wb = to_bf16x4(w);
-      if (p.algo == 2) {
-        multimem_st_f4(p.mc_params + i, w);
-        if (p.mc_shadow) multimem_st_bf16x4(p.mc_shadow + i, wb);
-      } else {
-#pragma unroll 4
-        for (int r = 0; r < p.world; ++r) {
-          *reinterpret_cast<float4*>(p.params[r] + i) = w;
-          if (p.shadow[r]) *reinterpret_cast<uint2*>(p.shadow[r] + i) = wb;
-        }
-      }
-    }
+    if (p.algo == 2) run_range<kNvls>(p, h, lo, hi);
+    else run_range<kTwoShot>(p, h, lo, hi);
   }
   // peers are done reading my grads (loads have retired: their values were consumed) and, in the
   // two-shot / nvls forms, done writing my params (needs the fence)
@@ -323,7 +337,7 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   long long vecs = p.count >> 2;
   if (p.world > 1 && p.algo != 0) vecs = (vecs + p.world - 1) / p.world;
   int grid = a->grid > 0 ? a->grid : 3 * 148;
-  // at least 4 vectors (64 bytes) per thread before another block (and its flag round) pays off
+  // one pass = 4 vectors (64 bytes) per thread; another block (and its flag round) pays off after that
   long long need = (vecs + 4 * block - 1) / (4 * block);
   if (need < 1) need = 1;
   if (grid > need) grid = (int)need;

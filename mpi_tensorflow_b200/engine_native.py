@@ -355,9 +355,12 @@ class NativeEngine:
             if not self.has_nvls:
                 raise RuntimeError("comm_algo='nvls' but no multicast mapping is available on this box")
             return 2
+        # measured crossovers (bench/allreduce_sweep.py, profiles/allreduce_sweep_*.jsonl): below
+        # 256 KB one flag round less wins; the in-switch reduction wins from 4 GPUs up, with 2 GPUs
+        # it has nothing to save and the plain two-shot is faster
         if count * 4 <= (256 << 10):
             return 0
-        return 2 if self.has_nvls else 1
+        return 2 if (self.has_nvls and self.world >= 4) else 1
 
     def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
                 advance: bool = True, grid: int = 0):
