@@ -49,7 +49,7 @@ class Step:
         torch.manual_seed(seed)
         c1, c2, fc, keep = PRESETS[model]
         self.net = MnistCnn(c1, c2, fc, keep).to(dev)
-        if os.environ.get("BASELINE_CHANNELS_LAST", "0") == "1":
+        if os.environ.get("BASELINE_CHANNELS_LAST", "1") == "1":
             self.net = self.net.to(memory_format=torch.channels_last)
         self.world, self.B, self.rows, self.dev = world, batch, rows, dev
         params = list(self.net.parameters())
