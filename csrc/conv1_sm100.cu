@@ -32,6 +32,12 @@ constexpr int X5_BYTES = X5_ROWS * 32;       // 29696
 constexpr int XS_PITCH = 33;
 constexpr int XS_FLOATS = 32 * XS_PITCH;     // padded 32x32 image, pitch 33
 
+// The reference's sequential batch window (mpipy.py:80-82) evaluated where the data is read:
+// rows [off, off+B) of the resident shard with off = (step*B) % (rows-B), step on the device.
+__device__ __forceinline__ long long window_offset(const long long* win_step, long long win_rows, int B) {
+  return win_step != nullptr ? ((*win_step) * (long long)B) % (win_rows - B) : 0;
+}
+
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
 // padded image -> shared floats; xs[i][j] = x[i-2][j-2] (zero outside).  NT threads, all loads issued first.
@@ -82,7 +88,8 @@ constexpr int kSmem = 1024 + kOffBar + 128;
 
 __global__ void __launch_bounds__(f1::kThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25][32]*/, const float* __restrict__ bias,
-                    bf16* __restrict__ out, uint8_t* __restrict__ idx, int B) {
+                    bf16* __restrict__ out, uint8_t* __restrict__ idx, int B, const long long* win_step,
+                    long long win_rows) {
   using namespace f1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -114,6 +121,7 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
   tc_fence_after();
   const uint32_t tmem = *holder;
   mtb::pdl_sync();
+  x += window_offset(win_step, win_rows, B) * (IMG * IMG);
   // per-kw weight tiles [32 c][16 kh] (K-major, SW32) from the fp32 master weights
   for (int i = threadIdx.x; i < 5 * C1; i += kThreads) {
     const int kw = i / C1, c = i % C1;
@@ -252,7 +260,8 @@ constexpr int kSmem = 1024 + kOffBar + 128;
 
 __global__ void __launch_bounds__(g1::kThreads, 1)
 conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, const bf16* __restrict__ P,
-                      const uint8_t* __restrict__ idx, float* __restrict__ dW, float* __restrict__ db, int B) {
+                      const uint8_t* __restrict__ idx, float* __restrict__ dW, float* __restrict__ db, int B,
+                      const long long* win_step, long long win_rows) {
   using namespace g1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -280,6 +289,7 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
   tc_fence_after();
   const uint32_t tmem = *holder;
   mtb::pdl_sync();
+  x += window_offset(win_step, win_rows, B) * (IMG * IMG);
 
   if (warp == 0) {
     if (elect_one()) {
@@ -406,25 +416,39 @@ extern "C" {
 // Tensor-core versions of mtb_conv1_fwd / mtb_conv1_wgrad (same arguments and output formats), C1 = 32.
 int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
                      cudaStream_t stream) {
+  return mtb_conv1_fwd_tc_win(x, w, bias, out_bf16, idx, B, nullptr, 0, stream);
+}
+
+// As above, but x is a resident shard of win_rows images and the batch is the reference's
+// sequential window for the step stored at *win_step (win_step == NULL: x is the batch itself).
+int mtb_conv1_fwd_tc_win(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                         const long long* win_step, long long win_rows, cudaStream_t stream) {
   MTB_REQUIRE(x && w && bias && out_bf16 && idx && B > 0, "conv1_fwd_tc: bad argument");
+  MTB_REQUIRE(win_step == nullptr || win_rows > B, "conv1_fwd_tc: shard must be larger than the batch");
   static bool attr = false;
   if (int e = set_smem(conv1_fwd_tc_kernel, f1::kSmem, &attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
   MTB_CUDA_CHECK(mtb::launch(conv1_fwd_tc_kernel, dim3(grid), dim3(f1::kThreads), (size_t)f1::kSmem, stream, x, w, bias,
-                             reinterpret_cast<bf16*>(out_bf16), idx, B));
+                             reinterpret_cast<bf16*>(out_bf16), idx, B, win_step, win_rows));
   return 0;
 }
 
 // dW and db are ACCUMULATED into (caller zeroes them once per step).
 int mtb_conv1_wgrad_tc(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
                        int B, cudaStream_t stream) {
+  return mtb_conv1_wgrad_tc_win(x, dP_bf16, P_bf16, idx, dW, db, B, nullptr, 0, stream);
+}
+
+int mtb_conv1_wgrad_tc_win(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW,
+                           float* db, int B, const long long* win_step, long long win_rows, cudaStream_t stream) {
   MTB_REQUIRE(x && dP_bf16 && P_bf16 && idx && dW && db && B > 0, "conv1_wgrad_tc: bad argument");
+  MTB_REQUIRE(win_step == nullptr || win_rows > B, "conv1_wgrad_tc: shard must be larger than the batch");
   static bool attr = false;
   if (int e = set_smem(conv1_wgrad_tc_kernel, g1::kSmem, &attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
   MTB_CUDA_CHECK(mtb::launch(conv1_wgrad_tc_kernel, dim3(grid), dim3(g1::kThreads), (size_t)g1::kSmem, stream, x,
                              reinterpret_cast<const bf16*>(dP_bf16), reinterpret_cast<const bf16*>(P_bf16), idx, dW, db,
-                             B));
+                             B, win_step, win_rows));
   return 0;
 }
 

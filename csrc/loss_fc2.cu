@@ -144,9 +144,10 @@ __global__ void __launch_bounds__(256)
 fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
                            const float* __restrict__ bias, const int* __restrict__ labels, float* __restrict__ logits,
                            float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ loss_accum,
-                           int* __restrict__ err_accum, int B, int F) {
+                           int* __restrict__ err_accum, int B, int F, const long long* win_step, long long win_rows) {
   extern __shared__ float sm[];
   pdl_sync();
+  if (labels != nullptr && win_step != nullptr) labels += ((*win_step) * (long long)B) % (win_rows - B);
   float* sW = sm;                                      // [F][NC]
   float* red = sm + (size_t)F * NC;                    // [8 warps][NC][32 rows]
   {
@@ -308,7 +309,16 @@ extern "C" {
 int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
                             float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
                             cudaStream_t stream) {
+  return mtb_fc2_softmax_ce_fast_win(h_bf16, W, bias, labels, logits, probs, dlogits, loss_accum, err_accum, B, F, NC,
+                                     nullptr, 0, stream);
+}
+
+// labels may be a resident shard of win_rows labels: the batch is the window of step *win_step (see conv1_sm100.cu)
+int mtb_fc2_softmax_ce_fast_win(const void* h_bf16, const float* W, const float* bias, const int* labels,
+                                float* logits, float* probs, float* dlogits, float* loss_accum, int* err_accum, int B,
+                                int F, int NC, const long long* win_step, long long win_rows, cudaStream_t stream) {
   MTB_REQUIRE(NC == 10 && F % 64 == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 64");
+  MTB_REQUIRE(win_step == nullptr || win_rows > B, "fc2_softmax_ce_fast: shard must be larger than the batch");
   const int smem = (F * NC + 8 * NC * 32) * (int)sizeof(float);
   MTB_REQUIRE(smem <= 200 * 1024, "fc2_softmax_ce_fast: weight matrix does not fit in shared memory");
   static int attr_bytes = 0;
@@ -318,7 +328,7 @@ int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bia
   }
   MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows_kernel<10>, dim3((B + 31) / 32), dim3(256), (size_t)smem, stream,
                              reinterpret_cast<const __nv_bfloat16*>(h_bf16), W, bias, labels, logits, probs, dlogits,
-                             loss_accum, err_accum, B, F));
+                             loss_accum, err_accum, B, F, win_step, win_rows));
   return 0;
 }
 

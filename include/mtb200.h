@@ -85,6 +85,16 @@ int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* ou
                      cudaStream_t stream);
 int mtb_conv1_wgrad_tc(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
                        int B, cudaStream_t stream);
+/* "_win" forms: x / labels are the rank's resident shard (win_rows rows) and the batch is the reference's sequential
+ * window offset = (step*B) % (rows-B) (mpipy.py:80-82) for the step stored on the device at *win_step, so a captured
+ * step needs neither a host feed nor a separate gather kernel.  win_step == NULL: the pointer is the batch itself. */
+int mtb_conv1_fwd_tc_win(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                         const long long* win_step, long long win_rows, cudaStream_t stream);
+int mtb_conv1_wgrad_tc_win(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW,
+                           float* db, int B, const long long* win_step, long long win_rows, cudaStream_t stream);
+int mtb_fc2_softmax_ce_fast_win(const void* h_bf16, const float* W, const float* bias, const int* labels,
+                                float* logits, float* probs, float* dlogits, float* loss_accum, int* err_accum, int B,
+                                int F, int NC, const long long* win_step, long long win_rows, cudaStream_t stream);
 
 /* ---- pooling + generic-conv helpers (mpipy.py:158,161; tf.nn.conv2d mpipy.py:159 via im2col) ---- */
 int mtb_maxpool2x2_fwd(const void* in, void* out, uint8_t* idx, int B, int H, int W, int C, cudaStream_t stream);

@@ -56,6 +56,7 @@ class NativeEngine:
         self.opt_step = 0
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_key = None
+        self._graphs: Dict[str, torch.cuda.CUDAGraph] = {}
         self._stream_state = None
         self.data_x = self.data_y = None
         self.rows = 0
@@ -123,6 +124,10 @@ class NativeEngine:
         self.dp1 = z(Bmax, 14, 14, s.c1)
         # conv1 on tensor cores when it has 32 output channels, else the CUDA-core kernel
         self.conv1_tc = s.c1 == 32 and self.conv_impl != "im2col"
+        self._fast_head = s.num_classes == 10 and s.fc % 64 == 0 and s.fc * 40 <= 190 * 1024
+        # batch window fused into the kernels that read the batch (needs both fast paths)
+        self._can_window = self.conv1_tc and self._fast_head
+        self._windowed = False
         # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
         want = self.conv_impl
         have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2))
@@ -190,11 +195,13 @@ class NativeEngine:
         self.data_x = x.to(self.device, dtype=torch.float32)
         self.data_y = torch.from_numpy(np.ascontiguousarray(shards.train_y)).to(self.device, dtype=torch.int32)
         self.rows = self.data_x.shape[0]
+        self._graphs.pop("window", None)         # that graph holds the old shard's address
         if not self.decay_rows:
             self.decay_rows = self.rows
 
     def attach_device_dataset(self, x: torch.Tensor, y: torch.Tensor):
         self.data_x, self.data_y, self.rows = x, y, x.shape[0]
+        self._graphs.pop("window", None)
         if not self.decay_rows:
             self.decay_rows = self.rows
 
@@ -212,14 +219,22 @@ class NativeEngine:
         self.y_in[:B].copy_(labels.reshape(B), non_blocking=True)
 
     # ------------------------------------------------------------------ forward
+    def _win(self):
+        """(images, labels, step pointer, rows) of the fused device-side batch window, or the
+        staged batch with a null step pointer."""
+        if self._windowed:
+            return self.data_x.data_ptr(), self.data_y.data_ptr(), self.dev_step.data_ptr(), self.rows
+        return self.x_in.data_ptr(), self.y_in.data_ptr(), None, 0
+
     def _forward(self, B: int, train: bool, with_loss: bool):
         s, c = self.spec, self.cfg
         P, S = self.P, self.S
         keep = s.keep_prob if (train and c.dropout) else 1.0
+        wx, wy, wstep, wrows = self._win()
         # conv1 + bias + ReLU + pool (mpipy.py:156-158)
         if self.conv1_tc:
-            N.call("mtb_conv1_fwd_tc", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(),
-                   P["conv1_bias"].data_ptr(), self.a1p.data_ptr(), self.idx1.data_ptr(), B)
+            N.call("mtb_conv1_fwd_tc_win", wx, P["conv1_weight"].data_ptr(),
+                   P["conv1_bias"].data_ptr(), self.a1p.data_ptr(), self.idx1.data_ptr(), B, wstep, wrows)
         else:
             N.call("mtb_conv1_fwd", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
                    self.a1p.data_ptr(), self.idx1.data_ptr(), B, s.c1)
@@ -240,11 +255,14 @@ class NativeEngine:
                     keep_prob=keep, seed=c.seed, step_ptr=self.dev_step,
                     bn=int(os.environ.get("MTB_FC1_BN", "0")) or (64 if B * s.fc < 96 * 128 * 128 else 128))
         # FC2 + softmax + CE + dlogits (mpipy.py:167, :55-56, :67)
-        N.call("mtb_fc2_softmax_ce_fast" if s.num_classes == 10 and s.fc % 64 == 0 and s.fc * 40 <= 190 * 1024 else "mtb_fc2_softmax_ce",
-               self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
-               self.y_in.data_ptr() if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
-               self.dlogits.data_ptr() if with_loss else None, self.loss_acc.data_ptr() if with_loss else None,
-               self.err_acc.data_ptr() if with_loss else None, B, s.fc, s.num_classes)
+        head = (self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
+                wy if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
+                self.dlogits.data_ptr() if with_loss else None, self.loss_acc.data_ptr() if with_loss else None,
+                self.err_acc.data_ptr() if with_loss else None, B, s.fc, s.num_classes)
+        if self._fast_head:
+            N.call("mtb_fc2_softmax_ce_fast_win", *head, wstep, wrows)
+        else:
+            N.call("mtb_fc2_softmax_ce", *head)
 
     # ------------------------------------------------------------------ backward
     def _backward(self, B: int):
@@ -299,8 +317,9 @@ class NativeEngine:
             N.call("mtb_col2im_5x5", self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
         # pool1 + ReLU backward fused into the conv1 weight gradient
         if self.conv1_tc:
-            N.call("mtb_conv1_wgrad_tc", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
-                   self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B)
+            wx, _, wstep, wrows = self._win()
+            N.call("mtb_conv1_wgrad_tc_win", wx, self.dp1.data_ptr(), self.a1p.data_ptr(),
+                   self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, wstep, wrows)
         else:
             N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
                    self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
@@ -381,6 +400,7 @@ class NativeEngine:
             self.stage_batch(x, y)
         else:
             self._window()
+        self._windowed = False
         self._zero_step_accumulators()
         self._forward(self.B, True, True)
         self._backward(self.B)
@@ -434,16 +454,26 @@ class NativeEngine:
         schedule runs on the device from the device step counter."""
         if images is not None:
             self.stage_batch(images, labels)
+            mode = "staged"
+        elif self._can_window:
+            if self.data_x is None:
+                raise RuntimeError("no resident dataset: call attach_dataset() or pass a batch")
+            mode = "window"                     # the kernels gather the window themselves
         else:
             self._window()
-        if self.cfg.cuda_graph:
-            if self._graph is None:
-                self._capture()
-            self._graph.replay()
-        else:
-            self._step_body()
+            mode = "staged"
+        self._run_step(mode)
         self.opt_step += 1
         return float(self.loss_acc.item()) if read_loss else 0.0
+
+    def _run_step(self, mode: str):
+        self._windowed = mode == "window"
+        if self.cfg.cuda_graph:
+            if mode not in self._graphs:
+                self._capture(mode)
+            self._graphs[mode].replay()
+        else:
+            self._step_body()
 
     # ------------------------------------------------------------------ host-streamed training
     def stream_steps(self, hx: torch.Tensor, hy: torch.Tensor, steps: int, ring: int = 4) -> List[float]:
@@ -479,8 +509,9 @@ class NativeEngine:
         copy = st["copy"]
         for ev in st["consumed"]:
             ev.record(main)
-        if self.cfg.cuda_graph and self._graph is None:
-            self._capture()
+        if self.cfg.cuda_graph and "staged" not in self._graphs:
+            self._windowed = False
+            self._capture("staged")
         losses: List[float] = []
         for i in range(steps):
             k, r = i & 1, i % ring
@@ -494,10 +525,7 @@ class NativeEngine:
             self.x_in[:B].copy_(st["x"][k], non_blocking=True)
             self.y_in[:B].copy_(st["y"][k], non_blocking=True)
             st["consumed"][k].record(main)
-            if self.cfg.cuda_graph:
-                self._graph.replay()
-            else:
-                self._step_body()
+            self._run_step("staged")
             if i >= ring:                                      # oldest slot of the ring: read it before reuse
                 st["loss_ev"][r].synchronize()
                 losses.append(float(st["loss"][r]))
@@ -510,8 +538,11 @@ class NativeEngine:
             losses.append(float(st["loss"][r]))
         return losses
 
-    def _capture(self):
-        """Warm up eagerly (sets kernel attributes, builds tensor maps), roll the state back, capture."""
+    def _capture(self, mode: str = "staged"):
+        """Warm up eagerly (sets kernel attributes, builds tensor maps), roll the state back, capture.
+        One graph per input mode: ``staged`` reads the batch buffers, ``window`` gathers the
+        resident shard's window inside the kernels."""
+        self._windowed = mode == "window"
         snap = [t.clone() for t in (self.flat_params, self.shadow, self.dev_step, *self.slots)]
         if self.p2p is not None:
             self.p2p.barrier()
@@ -529,6 +560,7 @@ class NativeEngine:
         with torch.cuda.graph(g, stream=self._side):
             self._step_body()
         self.launches_per_step = N.LAUNCHES - launches
+        self._graphs[mode] = g
         self._graph = g
         torch.cuda.synchronize()
 
@@ -540,6 +572,7 @@ class NativeEngine:
         if B > self.Bmax:
             raise ValueError(f"batch {B} exceeds the engine's static capacity {self.Bmax}")
         self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
+        self._windowed = False
         self._forward(B, dropout_step is not None, False)
         return self.probs[:B].clone()
 
@@ -560,3 +593,4 @@ class NativeEngine:
 
     def close(self):
         self._graph = None
+        self._graphs = {}
