@@ -226,6 +226,63 @@ conv2_fprop_pool_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   if (warp == 1) { tc_fence_after(); tmem_dealloc<256>(tmem); }
 }
 
+// The un-pooled gradient of one image, rebuilt in shared memory from the pooled maps (MaxPoolGrad
+// + ReluGrad, mpipy.py:160-161 backward): dflat / P / idx are [B,7,7,64]; the pooled gradient goes
+// to its argmax position if the pooled activation is positive, the other three positions of the
+// window get zero.  Pixel (h,w) lands in row base_row + 18h + w of a 128-byte-row SW128 tile whose
+// row 0 is 1 KiB aligned.  Replaces a separate kernel and a 25 MB round trip through HBM per step.
+struct PooledGrad { const bf16* dflat; const bf16* P; const uint8_t* idx; };
+
+template <int NT>
+struct DyItems {                                          // one image's share of a builder thread, in registers
+  static constexpr int PER = (49 * 8 + NT - 1) / NT;
+  uint4 g[PER], a[PER];
+  uint2 k[PER];
+  __device__ __forceinline__ void load(const PooledGrad& pg, int img, int t) {
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const int item = t + j * NT;
+      if (item < 49 * 8) {
+        const size_t o = ((size_t)img * 49 + (item >> 3)) * COUT + (item & 7) * 8;
+        g[j] = __ldg(reinterpret_cast<const uint4*>(pg.dflat + o));
+        a[j] = __ldg(reinterpret_cast<const uint4*>(pg.P + o));
+        k[j] = __ldg(reinterpret_cast<const uint2*>(pg.idx + o));
+      }
+    }
+  }
+  __device__ __forceinline__ void store(uint8_t* tile, int base_row, int t) const {
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const int item = t + j * NT;
+      if (item < 49 * 8) {
+        const int pp = item >> 3, chunk = item & 7;
+        const int ph = pp / 7, pw = pp % 7;
+        const uint32_t gw[4] = {g[j].x, g[j].y, g[j].z, g[j].w}, aw[4] = {a[j].x, a[j].y, a[j].z, a[j].w};
+        uint32_t kk[8], gm[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { kk[e] = (k[j].x >> (8 * e)) & 0xff; kk[4 + e] = (k[j].y >> (8 * e)) & 0xff; }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 av = mtb::unpack_bf16x2(aw[e]);
+          gm[e] = gw[e] & ((av.x > 0.f ? 0x0000ffffu : 0u) | (av.y > 0.f ? 0xffff0000u : 0u));
+        }
+#pragma unroll
+        for (int pos = 0; pos < 4; ++pos) {
+          uint4 v;
+          v.x = gm[0] & ((kk[0] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[1] == (uint32_t)pos ? 0xffff0000u : 0u));
+          v.y = gm[1] & ((kk[2] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[3] == (uint32_t)pos ? 0xffff0000u : 0u));
+          v.z = gm[2] & ((kk[4] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[5] == (uint32_t)pos ? 0xffff0000u : 0u));
+          v.w = gm[3] & ((kk[6] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[7] == (uint32_t)pos ? 0xffff0000u : 0u));
+          const int row = base_row + (2 * ph + (pos >> 1)) * PWID + 2 * pw + (pos & 1);
+          *reinterpret_cast<uint4*>(tile + row * 128 + ((chunk ^ (row & 7)) << 4)) = v;
+        }
+      }
+    }
+  }
+};
+
+constexpr int kBuilders = 256;                          // extra warps that build the dy tile in the fused variants
+
 // ======================================================================================= dgrad
 namespace dg {
 constexpr int kStages = 2;
@@ -236,9 +293,10 @@ constexpr int kOffBar = kOffPatch + kStages * kPatchBytes;
 constexpr int kSmem = 1024 + kOffBar + 128;
 }  // namespace dg
 
-__global__ void __launch_bounds__(kThreads, 1)
+template <bool kFused>
+__global__ void __launch_bounds__(kThreads + (kFused ? kBuilders : 0), 1)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_w,
-                   bf16* __restrict__ dx, int B) {
+                   bf16* __restrict__ dx, int B, const PooledGrad pg) {
   using namespace dg;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -256,9 +314,14 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
     tma_prefetch_desc(&map_dy);
     tma_prefetch_desc(&map_w);
     mbar_init(w_full, 1);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], 1); mbar_init(&p_empty[s], 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], kFused ? kBuilders : 1); mbar_init(&p_empty[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 4); }
     fence_barrier_init();
+  }
+  if (kFused) {       // halo rows and columns of both patch stages stay zero for the kernel's lifetime
+    for (int i = threadIdx.x; i < kStages * kPatchBytes / 16; i += blockDim.x)
+      reinterpret_cast<uint4*>(sPatch)[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async_smem();
   }
   if (warp == 1) tmem_alloc<128>(holder);
   tc_fence_before();
@@ -272,7 +335,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
       mbar_arrive_expect_tx(w_full, W_BYTES);
       for (int t = 0; t < TAPS; ++t) tma_load_2d(sW + t * 4096, &map_w, w_full, 0, t * CIN);
       int it = 0;
-      for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      for (int img = blockIdx.x; !kFused && img < B; img += gridDim.x, ++it) {
         const int s = it % kStages, ph = (it / kStages) & 1;
         mbar_wait(&p_empty[s], ph ^ 1);
         mbar_arrive_expect_tx(&p_full[s], PATCH_ROWS * 128);
@@ -280,6 +343,21 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
       }
     }
     __syncwarp();
+  } else if (kFused && warp >= kThreads / 32) {
+    // software pipeline: the next image's global loads are in flight while this one is written
+    const int t = threadIdx.x - kThreads;
+    DyItems<kBuilders> cur, nxt;
+    if ((int)blockIdx.x < B) nxt.load(pg, blockIdx.x, t);
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int s = it % kStages, ph = (it / kStages) & 1;
+      cur = nxt;
+      if (img + (int)gridDim.x < B) nxt.load(pg, img + gridDim.x, t);
+      mbar_wait(&p_empty[s], ph ^ 1);
+      cur.store(sPatch + s * kPatchBytes, 2 * PWID + 2, t);
+      fence_proxy_async_smem();
+      mbar_arrive(&p_full[s]);
+    }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, CIN, false, false);
@@ -293,17 +371,21 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
         tc_fence_after();
         const uint64_t a0 = make_smem_desc(smem_u32(sPatch + s * kPatchBytes), 16, 1024, kSwizzle128B);
         const uint64_t b0 = make_smem_desc(smem_u32(sW), 16, 1024, kSwizzle128B);
-#pragma unroll
-        for (int tile = 0; tile < 2; ++tile) {
+        // tap' = flipped tap: weight slot 24 - tap'.  Rolled over (tile, kh): 20 MMAs per trip with
+        // immediate offsets from two running descriptors keeps the issuing thread's registers low.
+#pragma unroll 1
+        for (int tk = 0; tk < 10; ++tk) {
+          const int tile = tk / 5, kh = tk % 5;
           const uint32_t d = tmem + a * 64 + tile * 32;
+          const uint64_t a_kh = a0 + (uint64_t)(((tile * 128 + kh * PWID) * 128) >> 4);
+          const uint64_t b_kh = b0 + (uint64_t)(((TAPS - 1 - kh * 5) * 4096) >> 4);
 #pragma unroll
-          for (int tap = 0; tap < TAPS; ++tap) {      // tap' = flipped tap: weight slot 24 - tap'
-            const int shift = (tap / 5) * PWID + (tap % 5);
+          for (int kw = 0; kw < 5; ++kw) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const uint64_t da = a0 + (uint64_t)(((tile * 128 + shift) * 128 + k * 32) >> 4);
-              const uint64_t db = b0 + (uint64_t)(((TAPS - 1 - tap) * 4096 + k * 32) >> 4);
-              if (tap == 0 && k == 0) mma_f16_first(d, da, db, idesc);
+              const uint64_t da = a_kh + (uint64_t)((kw * 128 + k * 32) >> 4);
+              const uint64_t db = b_kh - (uint64_t)((kw * 4096) >> 4) + (uint64_t)((k * 32) >> 4);
+              if (kw == 0 && k == 0 && kh == 0) mma_f16_first(d, da, db, idesc);
               else mma_f16_acc(d, da, db, idesc);
             }
           }
@@ -371,9 +453,10 @@ constexpr int kPartialFloats = kCols * 128;
 constexpr int kMaxPerGroup = 49;                           // 3 groups x 49 CTAs = 147 SMs
 }  // namespace wg
 
-__global__ void __launch_bounds__(kThreads, 1)
+template <bool kFused>
+__global__ void __launch_bounds__(kThreads + (kFused ? kBuilders : 0), 1)
 conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_dy,
-                   float* __restrict__ partial, float* __restrict__ db, int B) {
+                   float* __restrict__ partial, float* __restrict__ db, int B, const PooledGrad pg) {
   using namespace wg;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -386,13 +469,13 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 
   // guard rows must read as zero (0 * garbage could be NaN): clear everything once, TMA only ever
   // rewrites the data rows
-  for (int i = threadIdx.x; i < kStages * kStageBytes / 16; i += kThreads)
+  for (int i = threadIdx.x; i < kStages * kStageBytes / 16; i += blockDim.x)
     reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&map_x);
     tma_prefetch_desc(&map_dy);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], 1); mbar_init(&p_empty[s], 5); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], kFused ? 1 + kBuilders : 1); mbar_init(&p_empty[s], 5); }
     mbar_init(a_full, 1);
     fence_barrier_init();
   }
@@ -416,12 +499,30 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         const int s = it % kStages, ph = (it / kStages) & 1;
         mbar_wait(&p_empty[s], ph ^ 1);
         uint8_t* st = smem + s * kStageBytes;
-        mbar_arrive_expect_tx(&p_full[s], M_ROWS * 128 + PATCH_ROWS * 64);
-        tma_load_4d(st + kLead * 128, &map_dy, &p_full[s], 0, 0, 0, img);
+        if (kFused) {
+          mbar_arrive_expect_tx(&p_full[s], PATCH_ROWS * 64);
+        } else {
+          mbar_arrive_expect_tx(&p_full[s], M_ROWS * 128 + PATCH_ROWS * 64);
+          tma_load_4d(st + kLead * 128, &map_dy, &p_full[s], 0, 0, 0, img);
+        }
         tma_load_4d(st + kDyBytes, &map_x, &p_full[s], 0, -2, -2, img);
       }
     }
     __syncwarp();
+  } else if (kFused && warp >= kThreads / 32) {
+    const int t = threadIdx.x - kThreads;
+    DyItems<kBuilders> cur, nxt;
+    if (g_idx < B) nxt.load(pg, g_idx, t);
+    int it = 0;
+    for (int img = g_idx; img < B; img += g_cnt, ++it) {
+      const int s = it % kStages, ph = (it / kStages) & 1;
+      cur = nxt;
+      if (img + g_cnt < B) nxt.load(pg, img + g_cnt, t);
+      mbar_wait(&p_empty[s], ph ^ 1);
+      cur.store(smem + s * kStageBytes, kLead, t);
+      fence_proxy_async_smem();
+      mbar_arrive(&p_full[s]);
+    }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, 160, true, true);
@@ -598,9 +699,24 @@ int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int 
   CUtensorMap md, mw;
   MTB_REQUIRE(get_map(&md, dy_bf16, B, 1) && get_map(&mw, w_bf16, 0, 3), "conv2_dgrad: tensor map encode failed");
   static bool attr = false;
-  if (int e = set_smem(conv2_dgrad_kernel, dg::kSmem, &attr)) return e;
-  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel, dim3(grid_for(B)), dim3(kThreads), (size_t)dg::kSmem, stream, md, mw,
-                             reinterpret_cast<bf16*>(dx_bf16), B));
+  if (int e = set_smem(conv2_dgrad_kernel<false>, dg::kSmem, &attr)) return e;
+  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<false>, dim3(grid_for(B)), dim3(kThreads), (size_t)dg::kSmem, stream, md,
+                             mw, reinterpret_cast<bf16*>(dx_bf16), B, PooledGrad{nullptr, nullptr, nullptr}));
+  return 0;
+}
+
+// Same, with the MaxPoolGrad + ReluGrad in front of it fused in: takes the POOLED gradient dflat and the pooled
+// activation / argmax of the forward pass ([B,7,7,64] each) instead of the un-pooled gradient map.
+int mtb_conv2_dgrad_unpool(const void* dflat_bf16, const void* pooled_bf16, const uint8_t* idx, const void* w_bf16,
+                           void* dx_bf16, int B, cudaStream_t stream) {
+  MTB_REQUIRE(dflat_bf16 && pooled_bf16 && idx && w_bf16 && dx_bf16 && B > 0, "conv2_dgrad_unpool: bad argument");
+  CUtensorMap mw;
+  MTB_REQUIRE(get_map(&mw, w_bf16, 0, 3), "conv2_dgrad_unpool: tensor map encode failed");
+  static bool attr = false;
+  if (int e = set_smem(conv2_dgrad_kernel<true>, dg::kSmem, &attr)) return e;
+  const PooledGrad pg{reinterpret_cast<const bf16*>(dflat_bf16), reinterpret_cast<const bf16*>(pooled_bf16), idx};
+  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<true>, dim3(grid_for(B)), dim3(kThreads + kBuilders), (size_t)dg::kSmem,
+                             stream, mw, mw, reinterpret_cast<bf16*>(dx_bf16), B, pg));
   return 0;
 }
 
@@ -614,10 +730,28 @@ int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* d
   CUtensorMap mx, md;
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&md, dy_bf16, B, 2), "conv2_wgrad: tensor map encode failed");
   static bool attr = false;
-  if (int e = set_smem(conv2_wgrad_kernel, wg::kSmem, &attr)) return e;
+  if (int e = set_smem(conv2_wgrad_kernel<false>, wg::kSmem, &attr)) return e;
   const int grid = wgrad_grid(B);
-  MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_kernel, dim3(grid), dim3(kThreads), (size_t)wg::kSmem, stream, mx, md,
-                             reinterpret_cast<float*>(workspace), db, B));
+  MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_kernel<false>, dim3(grid), dim3(kThreads), (size_t)wg::kSmem, stream, mx, md,
+                             reinterpret_cast<float*>(workspace), db, B, PooledGrad{nullptr, nullptr, nullptr}));
+  MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_reduce_kernel, dim3((TAPS * CIN * COUT + 255) / 256), dim3(256), 0, stream,
+                             reinterpret_cast<const float*>(workspace), dW, grid));
+  return 0;
+}
+
+// Same, fed with the pooled gradient and the forward pass's pooled activation / argmax (see mtb_conv2_dgrad_unpool).
+int mtb_conv2_wgrad_unpool(const void* x_bf16, const void* dflat_bf16, const void* pooled_bf16, const uint8_t* idx,
+                           float* dW, float* db, void* workspace, int B, cudaStream_t stream) {
+  MTB_REQUIRE(x_bf16 && dflat_bf16 && pooled_bf16 && idx && dW && db && workspace && B > 0,
+              "conv2_wgrad_unpool: bad argument");
+  CUtensorMap mx;
+  MTB_REQUIRE(get_map(&mx, x_bf16, B, 0), "conv2_wgrad_unpool: tensor map encode failed");
+  static bool attr = false;
+  if (int e = set_smem(conv2_wgrad_kernel<true>, wg::kSmem, &attr)) return e;
+  const int grid = wgrad_grid(B);
+  const PooledGrad pg{reinterpret_cast<const bf16*>(dflat_bf16), reinterpret_cast<const bf16*>(pooled_bf16), idx};
+  MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_kernel<true>, dim3(grid), dim3(kThreads + kBuilders), (size_t)wg::kSmem, stream,
+                             mx, mx, reinterpret_cast<float*>(workspace), db, B, pg));
   MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_reduce_kernel, dim3((TAPS * CIN * COUT + 255) / 256), dim3(256), 0, stream,
                              reinterpret_cast<const float*>(workspace), dW, grid));
   return 0;

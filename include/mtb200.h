@@ -112,6 +112,11 @@ int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int 
 size_t mtb_conv2_wgrad_workspace_bytes(int B);
 int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* db, void* workspace, int B,
                     cudaStream_t stream);
+/* variants with MaxPoolGrad + ReluGrad fused in front: take the pooled gradient + pooled activation + argmax */
+int mtb_conv2_dgrad_unpool(const void* dflat_bf16, const void* pooled_bf16, const uint8_t* idx, const void* w_bf16,
+                           void* dx_bf16, int B, cudaStream_t stream);
+int mtb_conv2_wgrad_unpool(const void* x_bf16, const void* dflat_bf16, const void* pooled_bf16, const uint8_t* idx,
+                           float* dW, float* db, void* workspace, int B, cudaStream_t stream);
 /* probe of the shared-memory descriptor semantics the implicit-GEMM convolutions rely on (test only) */
 int mtb_debug_shift_mma(const void* A, const void* B, float* out, int mode, int row_bytes, int rows_total, int shift,
                         int base_off, cudaStream_t stream);

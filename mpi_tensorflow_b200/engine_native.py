@@ -298,16 +298,19 @@ class NativeEngine:
         s = self.spec
         P, S, G = self.P, self.S, self.G
         M2, K2 = B * 196, 25 * s.c1
-        # pool2 + ReLU backward (O19, O18), conv2 bias gradient
-        N.call("mtb_unpool_relu_bwd", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
-               self.da2.data_ptr(), B, 14, 14, s.c2)
-        da2 = self.da2.view(self.Bmax * 196, s.c2)
         if self.conv2_implicit:
-            # wgrad (+ bias grad) and dgrad as shift-GEMMs straight from the activation / gradient maps
-            N.call("mtb_conv2_wgrad", self.a1p.data_ptr(), da2.data_ptr(), G["conv2_weight"].data_ptr(),
-                   G["conv2_bias"].data_ptr(), self.c2_ws.data_ptr(), B)
-            N.call("mtb_conv2_dgrad", da2.data_ptr(), S["conv2_weight"].data_ptr(), self.dp1.data_ptr(), B)
+            # wgrad (+ bias grad) and dgrad as shift-GEMMs; pool2 + ReLU backward (O19, O18) is rebuilt
+            # inside both kernels from the pooled maps, so the un-pooled gradient never exists in HBM
+            N.call("mtb_conv2_wgrad_unpool", self.a1p.data_ptr(), self.dflat.data_ptr(), self.a2p.data_ptr(),
+                   self.idx2.data_ptr(), G["conv2_weight"].data_ptr(), G["conv2_bias"].data_ptr(),
+                   self.c2_ws.data_ptr(), B)
+            N.call("mtb_conv2_dgrad_unpool", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
+                   S["conv2_weight"].data_ptr(), self.dp1.data_ptr(), B)
         else:
+            # pool2 + ReLU backward (O19, O18), conv2 bias gradient
+            N.call("mtb_unpool_relu_bwd", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
+                   self.da2.data_ptr(), B, 14, 14, s.c2)
+            da2 = self.da2.view(self.Bmax * 196, s.c2)
             N.call("mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
             # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
             N.gemm_bf16(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,

@@ -79,6 +79,8 @@ _SIGS = {
     "mtb_conv2_fprop_pool": [vp, vp, vp, vp, vp, i32, vp],
     "mtb_conv2_dgrad": [vp, vp, vp, i32, vp],
     "mtb_conv2_wgrad": [vp, vp, vp, vp, vp, i32, vp],
+    "mtb_conv2_dgrad_unpool": [vp, vp, vp, vp, vp, i32, vp],
+    "mtb_conv2_wgrad_unpool": [vp, vp, vp, vp, vp, vp, vp, i32, vp],
 }
 
 

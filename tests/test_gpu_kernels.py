@@ -412,3 +412,35 @@ def test_conv2_wgrad_implicit_gemm(N, dev, B):
         ref = O.conv5x5_wgrad(x.cpu().float(), dy.cpu().float()).reshape(800, 64)
         assert _rel(dW.cpu(), ref) < 1e-4
         assert _rel(db.cpu(), dy.cpu().float().sum((0, 1, 2))) < 1e-4
+
+
+@pytest.mark.parametrize("B", [1, 6, 150, 297])
+def test_conv2_backward_with_fused_unpool(N, dev, B):
+    """dgrad / wgrad fed with the pooled gradient + argmax give what unpool -> dgrad / wgrad give."""
+    x = _bf(torch.relu(torch.randn(B, 14, 14, 32))).to(dev)
+    w = _bf(torch.randn(5, 5, 32, 64) * 0.05).to(dev)
+    a = _bf(torch.randn(B, 14, 14, 64))                      # pre-pool activation (after ReLU some are 0)
+    a = torch.relu(a)
+    p, i = O.maxpool2x2(a.float())
+    P = _bf(p).to(dev)
+    idx = i.to(torch.uint8).to(dev)
+    dflat = _bf(torch.randn(B, 7, 7, 64)).to(dev)
+    # reference path: separate un-pool kernel, then the plain kernels
+    dA = torch.zeros(B, 14, 14, 64, dtype=torch.bfloat16, device=dev)
+    N.call("mtb_unpool_relu_bwd", dflat.data_ptr(), P.data_ptr(), idx.data_ptr(), dA.data_ptr(), B, 14, 14, 64)
+    dx_ref = torch.zeros(B, 14, 14, 32, dtype=torch.bfloat16, device=dev)
+    N.call("mtb_conv2_dgrad", dA.data_ptr(), w.data_ptr(), dx_ref.data_ptr(), B)
+    ws = torch.zeros(N.lib().mtb_conv2_wgrad_workspace_bytes(B), dtype=torch.uint8, device=dev)
+    dW_ref, db_ref = torch.zeros(800, 64, device=dev), torch.zeros(64, device=dev)
+    N.call("mtb_conv2_wgrad", x.data_ptr(), dA.data_ptr(), dW_ref.data_ptr(), db_ref.data_ptr(), ws.data_ptr(), B)
+    # fused path
+    dx = torch.full((B, 14, 14, 32), 3.0, dtype=torch.bfloat16, device=dev)
+    N.call("mtb_conv2_dgrad_unpool", dflat.data_ptr(), P.data_ptr(), idx.data_ptr(), w.data_ptr(), dx.data_ptr(), B)
+    dW, db = torch.full((800, 64), float("nan"), device=dev), torch.zeros(64, device=dev)
+    N.call("mtb_conv2_wgrad_unpool", x.data_ptr(), dflat.data_ptr(), P.data_ptr(), idx.data_ptr(), dW.data_ptr(),
+           db.data_ptr(), ws.data_ptr(), B)
+    torch.cuda.synchronize()
+    assert torch.equal(dx, dx_ref)
+    assert _rel(dW, dW_ref) < 1e-5 and _rel(db, db_ref) < 1e-5
+    ref = O.conv5x5_dgrad(dA.cpu().float(), w.cpu().float(), (B, 14, 14, 32))
+    assert _rel(dx.cpu(), ref) < 5e-3
