@@ -26,6 +26,14 @@ namespace {
 using namespace sm100;
 using bf16 = __nv_bfloat16;
 
+// Optional role-level timeline of CTA 0 (build with -DMTB_TRACE): 8 slots per event row.
+#ifdef MTB_TRACE
+__device__ long long g_trace[64 * 16];
+#define TRACE(row, col) do { if (blockIdx.x == 0) g_trace[(row) * 16 + (col)] = clock64(); } while (0)
+#else
+#define TRACE(row, col) do { } while (0)
+#endif
+
 constexpr int IMG = 28, C1 = 32;
 constexpr int X5_ROWS = 928;                 // 896 + 32: kw shifts (<= 28 rows) of the last tile stay in bounds
 constexpr int X5_BYTES = X5_ROWS * 32;       // 29696
@@ -76,15 +84,42 @@ __device__ __forceinline__ void build_x5(uint8_t* x5, const float* xs, int t, in
 }
 
 // ======================================================================================= forward
+// Forward-pass row order of X5 ("planes"): a 2x2 pooling window must end up in ONE thread, so the
+// four window positions (dy,dx) become four separate accumulator tiles whose row r is the POOLED
+// pixel (ph = r/16, pw = r%16).  X5 is stored as four planes (dy, p): plane row 16*ph + q holds
+// pixel row h = 2ph+dy, padded column 2q+p.  Output position (dy,dx), tap kw reads padded column
+// 2pw+dx+kw, i.e. plane (dy, (dx+kw)&1) shifted by (dx+kw)>>1 rows: still a pure start-address
+// shift.  The epilogue thread of pooled pixel r loads its four accumulators and pools in
+// registers: no shuffles, no shared staging.
 namespace f1 {
 constexpr int kProducers = 128, kEpilogue = 256;            // kProducers per stage; one producer group per stage
 constexpr int kThreads = 32 + 2 * kProducers + kEpilogue;    // warp 0 MMA, 1-8 producers, 9-16 epilogue
+constexpr int kPlaneRows = 14 * 16;                          // 224
+constexpr int kX5Rows = 4 * kPlaneRows + 40;                 // tile 1 of the last plane reads up to row 3*224+255+2
+constexpr int kX5Bytes = ((kX5Rows * 32 + 1023) / 1024) * 1024;   // 30720
 constexpr int kOffX5 = 0;                                    // 2 stages
-constexpr int kOffW = 2 * X5_BYTES;                          // 5 x [32 c][16 kh] SW32 = 5 KB
+constexpr int kOffW = 2 * kX5Bytes;                          // 5 x [32 c][16 kh] SW32 = 5 KB
 constexpr int kOffXs = kOffW + 5 * 1024;                     // 2 x padded image
 constexpr int kOffBar = kOffXs + 2 * XS_FLOATS * 4;
 constexpr int kSmem = 1024 + kOffBar + 128;
 }  // namespace f1
+
+// X5 planes from the padded image.  Row R = 224*(2dy+p) + 16ph + q  <->  pixel row 2ph+dy, padded column 2q+p.
+__device__ __forceinline__ void build_x5_planes(uint8_t* x5, const float* xs, int t, int nthreads) {
+  for (int R = t; R < 4 * f1::kPlaneRows; R += nthreads) {
+    const int pl = R / f1::kPlaneRows, rr = R % f1::kPlaneRows;
+    const int dy = pl >> 1, p = pl & 1, ph = rr >> 4, q = rr & 15;
+    const float* src = xs + (2 * ph + dy) * XS_PITCH + 2 * q + p;
+    uint4 v;
+    v.x = mtb::pack_bf16x2(src[0], src[XS_PITCH]);
+    v.y = mtb::pack_bf16x2(src[2 * XS_PITCH], src[3 * XS_PITCH]);
+    v.z = mtb::pack_bf16x2(src[4 * XS_PITCH], 1.0f);
+    v.w = 0u;
+    const int sw = (R >> 2) & 1;                             // SW32: chunk ^= bit 7 of the byte address
+    *reinterpret_cast<uint4*>(x5 + R * 32 + (sw << 4)) = v;
+    *reinterpret_cast<uint4*>(x5 + R * 32 + ((sw ^ 1) << 4)) = make_uint4(0, 0, 0, 0);
+  }
+}
 
 __global__ void __launch_bounds__(f1::kThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25][32]*/, const float* __restrict__ bias,
@@ -103,8 +138,8 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
   uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // zero both X5 stages (tail rows and padding stay zero for the kernel's lifetime)
-  for (int i = threadIdx.x; i < 2 * X5_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(sX5)[i] = make_uint4(0, 0, 0, 0);
+  // zero both X5 stages (tail rows stay zero for the kernel's lifetime)
+  for (int i = threadIdx.x; i < 2 * kX5Bytes / 16; i += kThreads) reinterpret_cast<uint4*>(sX5)[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
@@ -143,23 +178,34 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
       int it = 0;
       for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
         const int s = it & 1, ph = (it >> 1) & 1;
+        TRACE(it, 0);
         mbar_wait(&x_full[s], ph);
+        TRACE(it, 1);
         mbar_wait(&a_empty[s], ph ^ 1);
+        TRACE(it, 2);
         tc_fence_after();
-        const uint64_t a0 = make_smem_desc(smem_u32(sX5 + s * X5_BYTES), 16, 256, kSwizzle32B);
+        const uint64_t a0 = make_smem_desc(smem_u32(sX5 + s * kX5Bytes), 16, 256, kSwizzle32B);
         const uint64_t b0 = make_smem_desc(smem_u32(sW), 16, 256, kSwizzle32B);
+        // accumulator (dy,dx,tile) lives in columns 32*(4dy + 2dx + tile) of this image's TMEM half
 #pragma unroll
-        for (int tile = 0; tile < 7; ++tile) {
+        for (int pos = 0; pos < 4; ++pos) {
+          const int dy = pos >> 1, dx = pos & 1;
 #pragma unroll
-          for (int kw = 0; kw < 5; ++kw) {
-            const uint64_t da = a0 + (uint64_t)(((tile * 128 + 4 * kw) * 32) >> 4);
-            const uint64_t db = b0 + (uint64_t)((kw * 1024) >> 4);
-            if (kw == 0) mma_f16_first(tmem + s * 256 + tile * 32, da, db, idesc);
-            else mma_f16_acc(tmem + s * 256 + tile * 32, da, db, idesc);
+          for (int tile = 0; tile < 2; ++tile) {
+            const uint32_t d = tmem + s * 256 + (pos * 2 + tile) * 32;
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const int row = (2 * dy + ((dx + kw) & 1)) * kPlaneRows + tile * 128 + ((dx + kw) >> 1);
+              const uint64_t da = a0 + (uint64_t)((row * 32) >> 4);
+              const uint64_t db = b0 + (uint64_t)((kw * 1024) >> 4);
+              if (kw == 0) mma_f16_first(d, da, db, idesc);
+              else mma_f16_acc(d, da, db, idesc);
+            }
           }
         }
         mma_commit(&x_empty[s]);
         mma_commit(&a_full[s]);
+        TRACE(it, 3);
       }
     }
     __syncwarp();
@@ -171,75 +217,67 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
     int it = g;
     for (int img = blockIdx.x + g * gridDim.x; img < B; img += 2 * gridDim.x, it += 2) {
       const int ph = (it >> 1) & 1;
-      mbar_wait(&x_empty[g], ph ^ 1);                        // MMAs that read this X5 stage have retired
-      load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);
+      if (t == 0) TRACE(it, 4);
+      load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);   // xs is this group's own: free since the last bar
       named_bar(2 + g, kProducers);                          // padded image complete
-      build_x5(sX5 + g * X5_BYTES, xs, t, kProducers);
+      mbar_wait(&x_empty[g], ph ^ 1);                        // MMAs that read this X5 stage have retired
+      if (t == 0) TRACE(it, 5);
+      build_x5_planes(sX5 + g * kX5Bytes, xs, t, kProducers);
       fence_proxy_async_smem();
       mbar_arrive(&x_full[g]);
+      if (t == 0) TRACE(it, 7);
       named_bar(2 + g, kProducers);                          // everyone is done reading xs
     }
   } else {
     const int q = warp & 3;
-    const int half = (warp - 9) >> 2;                        // tiles with tile % 2 == half
-    const int L = q * 32 + lane;                             // TMEM lane = row within a tile
-    const int wcol = L >> 2, hl = L & 3;
-    const int dy = hl & 1, dx = wcol & 1;
-    const uint32_t pos_key = 3u - (uint32_t)(2 * dy + dx);
-    float bs[32];
-#pragma unroll
-    for (int j = 0; j < 32; ++j) bs[j] = __ldg(bias + j);
+    const int tile = (warp - 9) >> 2;
+    const int r = tile * 128 + q * 32 + lane;                // pooled pixel of this thread
+    const int php = r >> 4, pwp = r & 15;
+    const bool valid = php < 14 && pwp < 14;
     int it = 0;
     for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
       const int s = it & 1, ph = (it >> 1) & 1;
+      if (warp == 9 && lane == 0) TRACE(it, 8);
       mbar_wait(&a_full[s], ph);
+      if (warp == 9 && lane == 0) TRACE(it, 9);
       tc_fence_after();
-#pragma unroll 1
-      for (int tile = half; tile < 7; tile += 2) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16) + s * 256 + tile * 32, r);
+      const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + s * 256 + tile * 32;
+      const size_t o = ((size_t)img * 196 + php * 14 + pwp) * C1;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {                 // 16 channels at a time keeps registers in check
+        uint32_t v[4][16];
+#pragma unroll
+        for (int pos = 0; pos < 4; ++pos) tmem_ld_32x16(tbase + pos * 64 + half * 16, v[pos]);
         tmem_ld_wait();
-        // key = relu(acc + bias) with the two low mantissa bits replaced by (3 - window position):
-        // an unsigned max picks the largest value and, on ties, the first position
-        uint32_t key[32];
+        uint32_t pk[8], ik[4];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float v = fmaxf(__uint_as_float(r[j]) + bs[j], 0.f);
-          key[j] = (__float_as_uint(v) & 0x7ffffffcu) | pos_key;          // also drops the sign of a -0.0
-        }
-        uint32_t m[16];
+        for (int j = 0; j < 16; j += 2) {
+          float val[2];
+          uint32_t arg[2];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const uint32_t send = dy ? key[j] : key[16 + j];
-          const uint32_t keep = dy ? key[16 + j] : key[j];
-          m[j] = max(keep, __shfl_xor_sync(0xffffffffu, send, 1));
+          for (int e = 0; e < 2; ++e) {
+            // value with its two low mantissa bits replaced by (3 - position): a float max picks the
+            // largest value and, among equal non-negative values, the first position
+            const float k0 = __uint_as_float((v[0][j + e] & ~3u) | 3u), k1 = __uint_as_float((v[1][j + e] & ~3u) | 2u);
+            const float k2 = __uint_as_float((v[2][j + e] & ~3u) | 1u), k3 = __uint_as_float(v[3][j + e] & ~3u);
+            const uint32_t m = __float_as_uint(fmaxf(fmaxf(k0, k1), fmaxf(k2, k3)));
+            val[e] = fmaxf(__uint_as_float(m & ~3u) + __ldg(bias + half * 16 + j + e), 0.f);   // relu(max + b) = max relu(. + b)
+            arg[e] = val[e] > 0.f ? 3u - (m & 3u) : 0u;      // an all-zero window reports position 0, like a first-max scan
+          }
+          pk[j >> 1] = mtb::pack_bf16x2(val[0], val[1]);
+          if ((j & 2) == 0) ik[j >> 2] = arg[0] | (arg[1] << 8);
+          else ik[j >> 2] |= (arg[0] << 16) | (arg[1] << 24);
         }
-        uint32_t f[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t send = dx ? m[j] : m[8 + j];
-          const uint32_t keep = dx ? m[8 + j] : m[j];
-          f[j] = max(keep, __shfl_xor_sync(0xffffffffu, send, 4));
-        }
-        if (wcol < IMG) {
-          const int h = tile * 4 + hl;
-          const int cbase = dy * 16 + dx * 8;
-          const size_t o = (((size_t)img * 14 + (h >> 1)) * 14 + (wcol >> 1)) * C1 + cbase;
-          uint4 pk;
-          pk.x = mtb::pack_bf16x2(__uint_as_float(f[0] & ~3u), __uint_as_float(f[1] & ~3u));
-          pk.y = mtb::pack_bf16x2(__uint_as_float(f[2] & ~3u), __uint_as_float(f[3] & ~3u));
-          pk.z = mtb::pack_bf16x2(__uint_as_float(f[4] & ~3u), __uint_as_float(f[5] & ~3u));
-          pk.w = mtb::pack_bf16x2(__uint_as_float(f[6] & ~3u), __uint_as_float(f[7] & ~3u));
-          *reinterpret_cast<uint4*>(out + o) = pk;
-          uint2 k2;
-          k2.x = (3u - (f[0] & 3u)) | ((3u - (f[1] & 3u)) << 8) | ((3u - (f[2] & 3u)) << 16) | ((3u - (f[3] & 3u)) << 24);
-          k2.y = (3u - (f[4] & 3u)) | ((3u - (f[5] & 3u)) << 8) | ((3u - (f[6] & 3u)) << 16) | ((3u - (f[7] & 3u)) << 24);
-          *reinterpret_cast<uint2*>(idx + o) = k2;
+        if (valid) {
+          *reinterpret_cast<uint4*>(out + o + half * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          *reinterpret_cast<uint4*>(out + o + half * 16 + 8) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          *reinterpret_cast<uint4*>(idx + o + half * 16) = make_uint4(ik[0], ik[1], ik[2], ik[3]);
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&a_empty[s]);
+      if (warp == 9 && lane == 0) TRACE(it, 10);
     }
   }
   __syncthreads();
@@ -412,6 +450,13 @@ int set_smem(K kern, int bytes, bool* done) {
 }  // namespace
 
 extern "C" {
+
+#ifdef MTB_TRACE
+int mtb_debug_trace_read(long long* host_out) {
+  MTB_CUDA_CHECK(cudaMemcpyFromSymbol(host_out, g_trace, sizeof(long long) * 64 * 16));
+  return 0;
+}
+#endif
 
 // Tensor-core versions of mtb_conv1_fwd / mtb_conv1_wgrad (same arguments and output formats), C1 = 32.
 int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,

@@ -37,6 +37,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "-Xptxas", "-v",
     "--expt-relaxed-constexpr",
+    *(["-DMTB_TRACE"] if os.environ.get("MTB_TRACE") else []),
     f"-I{INCLUDE}", f"-I{CSRC}",
 ]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread", f"-I{INCLUDE}"]
