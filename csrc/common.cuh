@@ -132,6 +132,26 @@ __device__ inline uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// MaxPoolGrad + ReluGrad on 8 channels with byte/halfword SIMD: g, a = 4 bf16x2 words each
+// (pooled gradient, pooled activation >= 0), k = 8 argmax bytes.  Returns the gradient words of
+// window position `pos`: the gradient where the argmax is `pos` and the activation is non-zero,
+// else 0.  A handful of integer ops instead of unpack / compare / select per channel.
+__device__ __forceinline__ void relu_mask_bf16x8(const uint4& g, const uint4& a, uint32_t (&gm)[4]) {
+  constexpr uint32_t kAbs = 0x7fff7fffu;          // a -0.0 out of a ReLU counts as zero
+  gm[0] = g.x & __vcmpne2(a.x & kAbs, 0u); gm[1] = g.y & __vcmpne2(a.y & kAbs, 0u);
+  gm[2] = g.z & __vcmpne2(a.z & kAbs, 0u); gm[3] = g.w & __vcmpne2(a.w & kAbs, 0u);
+}
+__device__ __forceinline__ uint4 route_to_pos_bf16x8(const uint32_t (&gm)[4], const uint2& k, uint32_t pos) {
+  const uint32_t p4 = pos * 0x01010101u;
+  const uint32_t m0 = __vcmpeq4(k.x, p4), m1 = __vcmpeq4(k.y, p4);        // 0xff per channel whose argmax is pos
+  uint4 v;
+  v.x = gm[0] & __byte_perm(m0, 0u, 0x1100);                               // bytes (b0,b0,b1,b1): one halfword per channel
+  v.y = gm[1] & __byte_perm(m0, 0u, 0x3322);
+  v.z = gm[2] & __byte_perm(m1, 0u, 0x1100);
+  v.w = gm[3] & __byte_perm(m1, 0u, 0x3322);
+  return v;
+}
+
 __device__ inline float2 unpack_bf16x2(uint32_t w) {
   __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&w);
   return __bfloat1622float2(v);

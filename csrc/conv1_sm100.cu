@@ -312,6 +312,7 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
   uint32_t* holder = reinterpret_cast<uint32_t*>(a_full + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+  if (threadIdx.x == 0) TRACE(30, 0);
   // X5 tails and the padding columns (w >= 28) of dA must read as zero for the whole kernel
   for (int i = threadIdx.x; i < (2 * X5_BYTES + 2 * DA_BYTES) / 16; i += kThreads)
     reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
@@ -326,7 +327,9 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *holder;
+  if (threadIdx.x == 0) TRACE(30, 1);
   mtb::pdl_sync();
+  if (threadIdx.x == 0) TRACE(30, 2);
   x += window_offset(win_step, win_rows, B) * (IMG * IMG);
 
   if (warp == 0) {
@@ -335,7 +338,9 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
       int it = 0;
       for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
         const int s = it & 1, ph = (it >> 1) & 1;
+        TRACE(16 + it, 0);
         mbar_wait(&x_full[s], ph);
+        TRACE(16 + it, 1);
         tc_fence_after();
         // A: 8 atoms of 16 (kh) one kw = 4 rows = 128 bytes apart; B: one 32-channel atom
         const uint64_t a0 = make_smem_desc(smem_u32(sX5 + s * X5_BYTES), 128, 256, kSwizzle32B);
@@ -346,6 +351,7 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
         for (int ks = 1; ks < 56; ++ks)
           mma_f16_acc(tmem, a0 + (uint64_t)((ks * 16 * 32) >> 4), b0 + (uint64_t)((ks * 16 * 64) >> 4), idesc);
         mma_commit(&x_empty[s]);
+        TRACE(16 + it, 2);
       }
       mma_commit(a_full);
     }
@@ -358,6 +364,7 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
     int it = g;
     for (int img = blockIdx.x + g * gridDim.x; img < B; img += 2 * gridDim.x, it += 2) {
       const int ph = (it >> 1) & 1;
+      if (t == 0) TRACE(16 + it, 4);
       // all global loads of this image first: pooled gradient, pooled activation, argmax (16+16+8 bytes
       // per 8 channels of a pooled pixel), then the padded input image
       constexpr int PER = (196 * 4 + kProducers - 1) / kProducers;      // 4 (the last one only for t < 16)
@@ -374,7 +381,9 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
         }
       }
       mbar_wait(&x_empty[g], ph ^ 1);
+      if (t == 0) TRACE(16 + it, 5);
       load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);
+      if (t == 0) TRACE(16 + it, 6);
       // dA rows of one pooling window: gradient goes to the argmax position if the pooled
       // activation is positive (ReLU), the other three positions get zero
 #pragma unroll
@@ -383,35 +392,23 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
         if (item < 196 * 4) {
           const int pp = item >> 2, chunk = item & 3;
           const int ph2 = pp / 14, pw = pp % 14;
-          const uint32_t gw[4] = {gq[k].x, gq[k].y, gq[k].z, gq[k].w}, aw[4] = {aq[k].x, aq[k].y, aq[k].z, aq[k].w};
-          uint32_t kk[8];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) { kk[e] = (kq[k].x >> (8 * e)) & 0xff; kk[4 + e] = (kq[k].y >> (8 * e)) & 0xff; }
           uint32_t gm[4];                                    // gradient with the ReLU mask applied, bf16x2
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float2 av = mtb::unpack_bf16x2(aw[e]);
-            gm[e] = gw[e] & ((av.x > 0.f ? 0x0000ffffu : 0u) | (av.y > 0.f ? 0xffff0000u : 0u));
-          }
+          mtb::relu_mask_bf16x8(gq[k], aq[k], gm);
 #pragma unroll
           for (int pos = 0; pos < 4; ++pos) {
-            uint4 v;
-            uint32_t o4[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-              o4[e] = gm[e] & ((kk[2 * e] == (uint32_t)pos ? 0x0000ffffu : 0u) |
-                               (kk[2 * e + 1] == (uint32_t)pos ? 0xffff0000u : 0u));
-            v.x = o4[0]; v.y = o4[1]; v.z = o4[2]; v.w = o4[3];
+            const uint4 v = mtb::route_to_pos_bf16x8(gm, kq[k], (uint32_t)pos);
             const int h = 2 * ph2 + (pos >> 1), wc = 2 * pw + (pos & 1);
             const int R = (h >> 2) * 128 + wc * 4 + (h & 3);
             *reinterpret_cast<uint4*>(da + R * 64 + ((chunk ^ ((R >> 1) & 3)) << 4)) = v;
           }
         }
       }
+      if (t == 0) TRACE(16 + it, 7);
       named_bar(2 + g, kProducers);                          // padded image complete
       build_x5(sX5 + g * X5_BYTES, xs, t, kProducers);
       fence_proxy_async_smem();
       mbar_arrive(&x_full[g]);
+      if (t == 0) TRACE(16 + it, 8);
       named_bar(2 + g, kProducers);                          // everyone is done reading xs
     }
   } else {
@@ -420,6 +417,7 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
     const int kw = L >> 4, kh = L & 15;
     if (blockIdx.x < B) {
       mbar_wait(a_full, 0);
+      if (L == 0) TRACE(30, 3);
       tc_fence_after();
       uint32_t r[32];
       tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16), r);
@@ -432,9 +430,11 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
         for (int c = 0; c < 32; ++c) atomicAdd(db + c, __uint_as_float(r[c]));
       }
       tc_fence_before();
+      if (L == 0) TRACE(30, 4);
     }
   }
   __syncthreads();
+  if (threadIdx.x == 0) TRACE(30, 5);
   if (warp == 0) { tc_fence_after(); tmem_dealloc<32>(tmem); }
 }
 

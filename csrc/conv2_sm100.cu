@@ -257,22 +257,11 @@ struct DyItems {                                          // one image's share o
       if (item < 49 * 8) {
         const int pp = item >> 3, chunk = item & 7;
         const int ph = pp / 7, pw = pp % 7;
-        const uint32_t gw[4] = {g[j].x, g[j].y, g[j].z, g[j].w}, aw[4] = {a[j].x, a[j].y, a[j].z, a[j].w};
-        uint32_t kk[8], gm[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) { kk[e] = (k[j].x >> (8 * e)) & 0xff; kk[4 + e] = (k[j].y >> (8 * e)) & 0xff; }
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 av = mtb::unpack_bf16x2(aw[e]);
-          gm[e] = gw[e] & ((av.x > 0.f ? 0x0000ffffu : 0u) | (av.y > 0.f ? 0xffff0000u : 0u));
-        }
+        uint32_t gm[4];
+        mtb::relu_mask_bf16x8(g[j], a[j], gm);
 #pragma unroll
         for (int pos = 0; pos < 4; ++pos) {
-          uint4 v;
-          v.x = gm[0] & ((kk[0] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[1] == (uint32_t)pos ? 0xffff0000u : 0u));
-          v.y = gm[1] & ((kk[2] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[3] == (uint32_t)pos ? 0xffff0000u : 0u));
-          v.z = gm[2] & ((kk[4] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[5] == (uint32_t)pos ? 0xffff0000u : 0u));
-          v.w = gm[3] & ((kk[6] == (uint32_t)pos ? 0x0000ffffu : 0u) | (kk[7] == (uint32_t)pos ? 0xffff0000u : 0u));
+          const uint4 v = mtb::route_to_pos_bf16x8(gm, k[j], (uint32_t)pos);
           const int row = base_row + (2 * ph + (pos >> 1)) * PWID + 2 * pw + (pos & 1);
           *reinterpret_cast<uint4*>(tile + row * 128 + ((chunk ^ (row & 7)) << 4)) = v;
         }
