@@ -121,10 +121,12 @@ __device__ __forceinline__ void build_x5_planes(uint8_t* x5, const float* xs, in
   }
 }
 
+struct ZeroList { void* ptr[8]; long long n_words[8]; int count; };
+
 __global__ void __launch_bounds__(f1::kThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25][32]*/, const float* __restrict__ bias,
                     bf16* __restrict__ out, uint8_t* __restrict__ idx, int B, const long long* win_step,
-                    long long win_rows) {
+                    long long win_rows, const ZeroList zl) {
   using namespace f1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -156,6 +158,12 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w /*[
   tc_fence_after();
   const uint32_t tmem = *holder;
   mtb::pdl_sync();
+  // first kernel of the step: clear the accumulators later kernels add into (they all run after this one)
+  for (int k = 0; k < zl.count; ++k) {
+    uint32_t* p = reinterpret_cast<uint32_t*>(zl.ptr[k]);
+    for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < zl.n_words[k]; i += (long long)gridDim.x * kThreads)
+      p[i] = 0u;
+  }
   x += window_offset(win_step, win_rows, B) * (IMG * IMG);
   // per-kw weight tiles [32 c][16 kh] (K-major, SW32) from the fp32 master weights
   for (int i = threadIdx.x; i < 5 * C1; i += kThreads) {
@@ -468,13 +476,23 @@ int mtb_conv1_fwd_tc(const float* x, const float* w, const float* bias, void* ou
 // sequential window for the step stored at *win_step (win_step == NULL: x is the batch itself).
 int mtb_conv1_fwd_tc_win(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
                          const long long* win_step, long long win_rows, cudaStream_t stream) {
+  return mtb_conv1_fwd_tc_win_zero(x, w, bias, out_bf16, idx, B, win_step, win_rows, nullptr, nullptr, 0, stream);
+}
+
+int mtb_conv1_fwd_tc_win_zero(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                              const long long* win_step, long long win_rows, void* const* zero_ptrs,
+                              const long long* zero_words, int zero_count, cudaStream_t stream) {
   MTB_REQUIRE(x && w && bias && out_bf16 && idx && B > 0, "conv1_fwd_tc: bad argument");
+  MTB_REQUIRE(zero_count >= 0 && zero_count <= 8, "conv1_fwd_tc: at most 8 ranges to clear");
+  ZeroList zl;
+  for (int k = 0; k < 8; ++k) { zl.ptr[k] = k < zero_count ? zero_ptrs[k] : nullptr; zl.n_words[k] = k < zero_count ? zero_words[k] : 0; }
+  zl.count = zero_count;
   MTB_REQUIRE(win_step == nullptr || win_rows > B, "conv1_fwd_tc: shard must be larger than the batch");
   static bool attr = false;
   if (int e = set_smem(conv1_fwd_tc_kernel, f1::kSmem, &attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
   MTB_CUDA_CHECK(mtb::launch(conv1_fwd_tc_kernel, dim3(grid), dim3(f1::kThreads), (size_t)f1::kSmem, stream, x, w, bias,
-                             reinterpret_cast<bf16*>(out_bf16), idx, B, win_step, win_rows));
+                             reinterpret_cast<bf16*>(out_bf16), idx, B, win_step, win_rows, zl));
   return 0;
 }
 

@@ -11,6 +11,13 @@ namespace {
 using namespace mtb;
 constexpr int kMaxClasses = 16;
 
+#ifdef MTB_TRACE
+__device__ long long g_trace2[64];
+#define TRACE2(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_trace2[i] = clock64(); } while (0)
+#else
+#define TRACE2(i) do { } while (0)
+#endif
+
 // one warp per row
 __global__ void __launch_bounds__(256)
 fc2_softmax_ce_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
@@ -139,8 +146,9 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
 // Forward: 32 rows per block, lane <-> row, the 8 warps split the features; W sits in shared
 // memory and every read of it is a warp-wide broadcast, so the loop is pure FMA.  Loss and error
 // count are reduced inside the block first: one atomic per block instead of one per row.
+constexpr int kHeadWarps = 16;
 template <int NC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kHeadWarps * 32)
 fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
                            const float* __restrict__ bias, const int* __restrict__ labels, float* __restrict__ logits,
                            float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ loss_accum,
@@ -149,7 +157,7 @@ fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __r
   pdl_sync();
   if (labels != nullptr && win_step != nullptr) labels += ((*win_step) * (long long)B) % (win_rows - B);
   float* sW = sm;                                      // [F][NC]
-  float* red = sm + (size_t)F * NC;                    // [8 warps][NC][32 rows]
+  float* red = sm + (size_t)F * NC;                    // [kHeadWarps][NC][32 rows]
   {
     const float4* src = reinterpret_cast<const float4*>(W);
     float4* dst = reinterpret_cast<float4*>(sW);
@@ -158,13 +166,13 @@ fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __r
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 32 + lane;
-  const int fper = F / 8, fbeg = warp * fper;
+  const int fper = F / kHeadWarps, fbeg = warp * fper;
   float acc[NC];
 #pragma unroll
   for (int c = 0; c < NC; ++c) acc[c] = 0.f;
   if (row < B) {
     const uint4* hr = reinterpret_cast<const uint4*>(h + (size_t)row * F + fbeg);
-#pragma unroll 4
+#pragma unroll 8
     for (int i = 0; i < fper / 8; ++i) {
       const uint4 pk = __ldg(hr + i);
       const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
@@ -190,7 +198,7 @@ fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __r
   for (int c = 0; c < NC; ++c) {
     float s = __ldg(bias + c);
 #pragma unroll
-    for (int w = 0; w < 8; ++w) s += red[(w * NC + c) * 32 + lane];
+    for (int w = 0; w < kHeadWarps; ++w) s += red[(w * NC + c) * 32 + lane];
     lg[c] = s;
     mx = fmaxf(mx, s);
   }
@@ -234,7 +242,9 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
                      const float* __restrict__ W /*[F,NC]*/, __nv_bfloat16* __restrict__ dh, float* __restrict__ dW,
                      float* __restrict__ db2, float* __restrict__ db1, int B, int F, float scale, int rows_per_block) {
   extern __shared__ float sm[];                        // dl [rows_per_block][NC], then the reduction buffer
+  TRACE2(0);
   pdl_sync();
+  TRACE2(1);
   float* sdl = sm;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int f0 = blockIdx.x * 64 + lane * 2;
@@ -250,30 +260,44 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
   }
   float cs0 = 0.f, cs1 = 0.f;
   __syncthreads();
+  TRACE2(2);
   if (f0 < F) {
-    for (int r = warp; r < nrows; r += 8) {
-      const float* dl = sdl + r * NC;
-      const size_t o = (size_t)(b0 + r) * F + f0;
-      const float2 hv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(h + o));
-      float t0 = 0.f, t1 = 0.f;
+    // 4 rows per pass, their loads issued together (the loop is latency-bound otherwise)
+    for (int r0 = warp; r0 < nrows; r0 += 32) {
+      __nv_bfloat162 hq[4];
 #pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        const float d = dl[c];
-        t0 = fmaf(d, w0[c], t0);
-        t1 = fmaf(d, w1[c], t1);
-        a0[c] = fmaf(hv.x, d, a0[c]);
-        a1[c] = fmaf(hv.y, d, a1[c]);
+      for (int u = 0; u < 4; ++u) {
+        const int r = r0 + 8 * u;
+        if (r < nrows) hq[u] = *reinterpret_cast<const __nv_bfloat162*>(h + (size_t)(b0 + r) * F + f0);
       }
-      t0 = hv.x > 0.f ? t0 * scale : 0.f;
-      t1 = hv.y > 0.f ? t1 * scale : 0.f;
-      const __nv_bfloat162 q = __floats2bfloat162_rn(t0, t1);
-      *reinterpret_cast<__nv_bfloat162*>(dh + o) = q;
-      const float2 qf = __bfloat1622float2(q);           // bias gradient of FC1 sums what FC1's wgrad will see
-      cs0 += qf.x;
-      cs1 += qf.y;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int r = r0 + 8 * u;
+        if (r >= nrows) break;
+        const float* dl = sdl + r * NC;
+        const size_t o = (size_t)(b0 + r) * F + f0;
+        const float2 hv = __bfloat1622float2(hq[u]);
+        float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const float d = dl[c];
+          t0 = fmaf(d, w0[c], t0);
+          t1 = fmaf(d, w1[c], t1);
+          a0[c] = fmaf(hv.x, d, a0[c]);
+          a1[c] = fmaf(hv.y, d, a1[c]);
+        }
+        t0 = hv.x > 0.f ? t0 * scale : 0.f;
+        t1 = hv.y > 0.f ? t1 * scale : 0.f;
+        const __nv_bfloat162 q = __floats2bfloat162_rn(t0, t1);
+        *reinterpret_cast<__nv_bfloat162*>(dh + o) = q;
+        const float2 qf = __bfloat1622float2(q);         // bias gradient of FC1 sums what FC1's wgrad will see
+        cs0 += qf.x;
+        cs1 += qf.y;
+      }
     }
   }
   __syncthreads();                                      // everyone is done with sdl
+  TRACE2(3);
   float* red = sm;                                      // [8 warps][2*NC+2][32 lanes]
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
@@ -295,16 +319,25 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
     else if (k == 2 * NC) atomicAdd(db1 + f, s);
     else if (f + 1 < F) atomicAdd(db1 + f + 1, s);
   }
+  TRACE2(4);
   if (blockIdx.x == 0 && threadIdx.x < NC) {            // FC2 bias gradient: column sums of dlogits
     float s = 0.f;
     for (int r = 0; r < nrows; ++r) s += dlogits[(size_t)(b0 + r) * NC + threadIdx.x];
     atomicAdd(db2 + threadIdx.x, s);
   }
+  TRACE2(5);
 }
 
 }  // namespace
 
 extern "C" {
+
+#ifdef MTB_TRACE
+int mtb_debug_trace2_read(long long* host_out) {
+  MTB_CUDA_CHECK(cudaMemcpyFromSymbol(host_out, g_trace2, sizeof(long long) * 64));
+  return 0;
+}
+#endif
 
 int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,
                             float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
@@ -317,16 +350,16 @@ int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bia
 int mtb_fc2_softmax_ce_fast_win(const void* h_bf16, const float* W, const float* bias, const int* labels,
                                 float* logits, float* probs, float* dlogits, float* loss_accum, int* err_accum, int B,
                                 int F, int NC, const long long* win_step, long long win_rows, cudaStream_t stream) {
-  MTB_REQUIRE(NC == 10 && F % 64 == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 64");
+  MTB_REQUIRE(NC == 10 && F % (8 * kHeadWarps) == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 128");
   MTB_REQUIRE(win_step == nullptr || win_rows > B, "fc2_softmax_ce_fast: shard must be larger than the batch");
-  const int smem = (F * NC + 8 * NC * 32) * (int)sizeof(float);
+  const int smem = (F * NC + kHeadWarps * NC * 32) * (int)sizeof(float);
   MTB_REQUIRE(smem <= 200 * 1024, "fc2_softmax_ce_fast: weight matrix does not fit in shared memory");
   static int attr_bytes = 0;
   if (smem > attr_bytes) {
     MTB_CUDA_CHECK(cudaFuncSetAttribute(fc2_softmax_ce_rows_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_bytes = smem;
   }
-  MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows_kernel<10>, dim3((B + 31) / 32), dim3(256), (size_t)smem, stream,
+  MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows_kernel<10>, dim3((B + 31) / 32), dim3(kHeadWarps * 32), (size_t)smem, stream,
                              reinterpret_cast<const __nv_bfloat16*>(h_bf16), W, bias, labels, logits, probs, dlogits,
                              loss_accum, err_accum, B, F, win_step, win_rows));
   return 0;
@@ -338,7 +371,8 @@ int mtb_fc2_bwd_fused(const void* h_bf16, const float* dlogits, const float* W, 
   MTB_REQUIRE(NC == 10 && F % 2 == 0, "fc2_bwd_fused: 10 classes, even F");
   int splits = 1;
   const int fx = (F + 63) / 64;
-  while (fx * splits < 128 && B / (splits * 2) >= 32) splits *= 2;
+  // two blocks (16 warps) per SM: the row loop is a dependent FMA chain and needs the extra warps to hide latency
+  while (fx * splits < 256 && B / (splits * 2) >= 32) splits *= 2;
   const int rows_per_block = (B + splits - 1) / splits;
   const int smem = (int)sizeof(float) * (rows_per_block * NC > 8 * 22 * 32 ? rows_per_block * NC : 8 * 22 * 32);
   MTB_REQUIRE(smem <= 48 * 1024, "fc2_bwd_fused: batch slice too large");

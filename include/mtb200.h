@@ -90,6 +90,11 @@ int mtb_conv1_wgrad_tc(const float* x, const void* dP_bf16, const void* P_bf16, 
  * step needs neither a host feed nor a separate gather kernel.  win_step == NULL: the pointer is the batch itself. */
 int mtb_conv1_fwd_tc_win(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
                          const long long* win_step, long long win_rows, cudaStream_t stream);
+/* ... and, being the first kernel of a step, it can also clear the step's accumulators (up to 8 ranges of 32-bit
+ * words, as mtb_zero_multi) so that no separate launch is needed for that */
+int mtb_conv1_fwd_tc_win_zero(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B,
+                              const long long* win_step, long long win_rows, void* const* zero_ptrs,
+                              const long long* zero_words, int zero_count, cudaStream_t stream);
 int mtb_conv1_wgrad_tc_win(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW,
                            float* db, int B, const long long* win_step, long long win_rows, cudaStream_t stream);
 int mtb_fc2_softmax_ce_fast_win(const void* h_bf16, const float* W, const float* bias, const int* labels,

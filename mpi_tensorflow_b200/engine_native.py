@@ -124,7 +124,7 @@ class NativeEngine:
         self.dp1 = z(Bmax, 14, 14, s.c1)
         # conv1 on tensor cores when it has 32 output channels, else the CUDA-core kernel
         self.conv1_tc = s.c1 == 32 and self.conv_impl != "im2col"
-        self._fast_head = s.num_classes == 10 and s.fc % 64 == 0 and s.fc * 40 <= 190 * 1024
+        self._fast_head = s.num_classes == 10 and s.fc % 128 == 0 and s.fc * 40 <= 170 * 1024
         # batch window fused into the kernels that read the batch (needs both fast paths)
         self._can_window = self.conv1_tc and self._fast_head
         self._windowed = False
@@ -226,13 +226,18 @@ class NativeEngine:
             return self.data_x.data_ptr(), self.data_y.data_ptr(), self.dev_step.data_ptr(), self.rows
         return self.x_in.data_ptr(), self.y_in.data_ptr(), None, 0
 
-    def _forward(self, B: int, train: bool, with_loss: bool):
+    def _forward(self, B: int, train: bool, with_loss: bool, zero: bool = False):
         s, c = self.spec, self.cfg
         P, S = self.P, self.S
         keep = s.keep_prob if (train and c.dropout) else 1.0
         wx, wy, wstep, wrows = self._win()
         # conv1 + bias + ReLU + pool (mpipy.py:156-158)
-        if self.conv1_tc:
+        if self.conv1_tc and zero:
+            # the step's first kernel also clears the accumulators the backward kernels add into
+            ptrs, words, nz = self._zero_list()
+            N.call("mtb_conv1_fwd_tc_win_zero", wx, P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
+                   self.a1p.data_ptr(), self.idx1.data_ptr(), B, wstep, wrows, ptrs, words, nz)
+        elif self.conv1_tc:
             N.call("mtb_conv1_fwd_tc_win", wx, P["conv1_weight"].data_ptr(),
                    P["conv1_bias"].data_ptr(), self.a1p.data_ptr(), self.idx1.data_ptr(), B, wstep, wrows)
         else:
@@ -327,13 +332,20 @@ class NativeEngine:
             N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
                    self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
 
-    def _zero_step_accumulators(self):
+    def _zero_list(self):
+        if self._zero_args is None:
+            self._zero_step_accumulators(build_only=True)
+        return self._zero_args
+
+    def _zero_step_accumulators(self, build_only: bool = False):
         if self._zero_args is None:
             items = [(self.flat_grads[lo:hi].data_ptr(), hi - lo) for lo, hi in self._zero_ranges if hi > lo]
             items += [(self.loss_acc.data_ptr(), 1), (self.err_acc.data_ptr(), 1)]
             ptrs = (C.c_void_p * 8)(*[p for p, _ in items])
             words = (C.c_longlong * 8)(*[n for _, n in items])
             self._zero_args = (ptrs, words, len(items))
+        if build_only:
+            return
         ptrs, words, n = self._zero_args
         N.call("mtb_zero_multi", ptrs, words, n)
 
@@ -430,8 +442,11 @@ class NativeEngine:
         return loss
 
     def _step_body(self):
-        self._zero_step_accumulators()
-        self._forward(self.B, True, True)
+        if self.conv1_tc:
+            self._forward(self.B, True, True, zero=True)
+        else:
+            self._zero_step_accumulators()
+            self._forward(self.B, True, True)
         if not self.cfg.overlap:
             self._backward(self.B)
             self._update(peers=True)

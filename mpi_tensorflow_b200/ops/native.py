@@ -59,6 +59,7 @@ _SIGS = {
     "mtb_conv1_fwd_tc": [vp, vp, vp, vp, vp, i32, vp],
     "mtb_conv1_wgrad_tc": [vp, vp, vp, vp, vp, vp, i32, vp],
     "mtb_conv1_fwd_tc_win": [vp, vp, vp, vp, vp, i32, vp, i64, vp],
+    "mtb_conv1_fwd_tc_win_zero": [vp, vp, vp, vp, vp, i32, vp, i64, vp, vp, i32, vp],
     "mtb_conv1_wgrad_tc_win": [vp, vp, vp, vp, vp, vp, i32, vp, i64, vp],
     "mtb_fc2_softmax_ce_fast_win": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, i64, vp],
     "mtb_maxpool2x2_fwd": [vp, vp, vp, i32, i32, i32, i32, vp],
