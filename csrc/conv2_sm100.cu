@@ -278,12 +278,24 @@ constexpr int kStages = 2;
 constexpr int kPatchBytes = 336 * 128;
 constexpr int kOffW = 0;
 constexpr int kOffPatch = W_BYTES;
-constexpr int kOffBar = kOffPatch + kStages * kPatchBytes;
+constexpr int kOffBnd = kOffPatch + kStages * kPatchBytes;   // fp32 [5 sources][4 kw][4 lanes][32 ci] boundary rows
+constexpr int kBndFloats = 4 * 4 * 32;                       // per source (4 warps of the tile + the carry from tile 1)
+constexpr int kOffBar = kOffBnd + 5 * kBndFloats * 4;
 constexpr int kSmem = 1024 + kOffBar + 128;
 }  // namespace dg
 
+// dgrad with the horizontal taps folded into the MMA's N dimension:
+//   E[r, (kw,ci)] = sum_kh sum_co patch[r + 18 kh][co] . W'[kh][kw][ci][co]         20 MMAs (128 x 160 x 16) per tile
+//   dx[m, ci]     = sum_kw E[m + kw, (kw,ci)]
+// instead of 100 MMAs with N = 32: shared-memory operand traffic per FLOP drops ~2.4x, which is what
+// bounds these kernels.  The row shift of the final sum is a lane shift: shuffles inside a warp, a
+// small shared-memory hand-over for the last four lanes of each warp (tile 1 is issued first so
+// that its leading rows are there when tile 0's last warp needs them).
+constexpr int kThreadsD = 64 + 256;                      // dgrad: TMA warp, MMA warp, 8 epilogue warps
+constexpr int kBuildersD = 128;
+
 template <bool kFused>
-__global__ void __launch_bounds__(kThreads + (kFused ? kBuilders : 0), 1)
+__global__ void __launch_bounds__(kThreadsD + (kFused ? kBuildersD : 0), 1)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_w,
                    bf16* __restrict__ dx, int B, const PooledGrad pg) {
   using namespace dg;
@@ -291,10 +303,11 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = smem + kOffW;
   uint8_t* sPatch = smem + kOffPatch;
+  float* sBnd = reinterpret_cast<float*>(smem + kOffBnd);
   uint64_t* w_full = reinterpret_cast<uint64_t*>(smem + kOffBar);
   uint64_t* p_full = w_full + 1;
   uint64_t* p_empty = p_full + kStages;
-  uint64_t* a_full = p_empty + kStages;
+  uint64_t* a_full = p_empty + kStages;         // one per accumulator buffer (a buffer holds ONE tile, 160 columns)
   uint64_t* a_empty = a_full + 2;
   uint32_t* holder = reinterpret_cast<uint32_t*>(a_empty + 2);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -303,8 +316,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
     tma_prefetch_desc(&map_dy);
     tma_prefetch_desc(&map_w);
     mbar_init(w_full, 1);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], kFused ? kBuilders : 1); mbar_init(&p_empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 4); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&p_full[s], kFused ? kBuildersD : 1); mbar_init(&p_empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&a_full[a], 1); mbar_init(&a_empty[a], 8); }
     fence_barrier_init();
   }
   if (kFused) {       // halo rows and columns of both patch stages stay zero for the kernel's lifetime
@@ -312,7 +325,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
       reinterpret_cast<uint4*>(sPatch)[i] = make_uint4(0, 0, 0, 0);
     fence_proxy_async_smem();
   }
-  if (warp == 1) tmem_alloc<128>(holder);
+  if (warp == 1) tmem_alloc<512>(holder);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -321,8 +334,10 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
 
   if (warp == 0) {
     if (lane == 0) {
+      // tap t goes to slot 24 - t: slot s then holds the FLIPPED tap s, and the five kw of one kh are
+      // 160 consecutive K-major rows (one N = 160 operand)
       mbar_arrive_expect_tx(w_full, W_BYTES);
-      for (int t = 0; t < TAPS; ++t) tma_load_2d(sW + t * 4096, &map_w, w_full, 0, t * CIN);
+      for (int t = 0; t < TAPS; ++t) tma_load_2d(sW + (TAPS - 1 - t) * 4096, &map_w, w_full, 0, t * CIN);
       int it = 0;
       for (int img = blockIdx.x; !kFused && img < B; img += gridDim.x, ++it) {
         const int s = it % kStages, ph = (it / kStages) & 1;
@@ -332,10 +347,10 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
       }
     }
     __syncwarp();
-  } else if (kFused && warp >= kThreads / 32) {
+  } else if (kFused && warp >= kThreadsD / 32) {
     // software pipeline: the next image's global loads are in flight while this one is written
-    const int t = threadIdx.x - kThreads;
-    DyItems<kBuilders> cur, nxt;
+    const int t = threadIdx.x - kThreadsD;
+    DyItems<kBuildersD> cur, nxt;
     if ((int)blockIdx.x < B) nxt.load(pg, blockIdx.x, t);
     int it = 0;
     for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
@@ -349,79 +364,123 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_cons
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, CIN, false, false);
+      constexpr uint32_t idesc = make_idesc(kFmtBF16, 128, 5 * CIN, false, false);
       mbar_wait(w_full, 0);
-      int it = 0;
+      int it = 0, n = 0;                               // n counts tiles: buffer n & 1
       for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
         const int s = it % kStages, ph = (it / kStages) & 1;
-        const int a = it & 1, aph = (it >> 1) & 1;
         mbar_wait(&p_full[s], ph);
-        mbar_wait(&a_empty[a], aph ^ 1);
-        tc_fence_after();
         const uint64_t a0 = make_smem_desc(smem_u32(sPatch + s * kPatchBytes), 16, 1024, kSwizzle128B);
         const uint64_t b0 = make_smem_desc(smem_u32(sW), 16, 1024, kSwizzle128B);
-        // tap' = flipped tap: weight slot 24 - tap'.  Rolled over (tile, kh): 20 MMAs per trip with
-        // immediate offsets from two running descriptors keeps the issuing thread's registers low.
 #pragma unroll 1
-        for (int tk = 0; tk < 10; ++tk) {
-          const int tile = tk / 5, kh = tk % 5;
-          const uint32_t d = tmem + a * 64 + tile * 32;
-          const uint64_t a_kh = a0 + (uint64_t)(((tile * 128 + kh * PWID) * 128) >> 4);
-          const uint64_t b_kh = b0 + (uint64_t)(((TAPS - 1 - kh * 5) * 4096) >> 4);
+        for (int tt = 0; tt < 2; ++tt, ++n) {          // tile 1 first, then tile 0
+          const int tile = 1 - tt;
+          const int a = n & 1, aph = (n >> 1) & 1;
+          mbar_wait(&a_empty[a], aph ^ 1);
+          tc_fence_after();
+          const uint32_t d = tmem + a * 256;
 #pragma unroll
-          for (int kw = 0; kw < 5; ++kw) {
+          for (int kh = 0; kh < 5; ++kh) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const uint64_t da = a_kh + (uint64_t)((kw * 128 + k * 32) >> 4);
-              const uint64_t db = b_kh - (uint64_t)((kw * 4096) >> 4) + (uint64_t)((k * 32) >> 4);
-              if (kw == 0 && k == 0 && kh == 0) mma_f16_first(d, da, db, idesc);
+              const uint64_t da = a0 + (uint64_t)(((tile * 128 + kh * PWID) * 128 + k * 32) >> 4);
+              const uint64_t db = b0 + (uint64_t)((kh * 5 * 4096 + k * 32) >> 4);
+              if (kh == 0 && k == 0) mma_f16_first(d, da, db, idesc);
               else mma_f16_acc(d, da, db, idesc);
             }
           }
+          if (tt == 1) mma_commit(&p_empty[s]);
+          mma_commit(&a_full[a]);
         }
-        mma_commit(&p_empty[s]);
-        mma_commit(&a_full[a]);
       }
     }
     __syncwarp();
   } else {
+    // 8 epilogue warps: warp % 4 = TMEM lane quadrant, (warp - 2) / 4 = which 16 of the 32 channels
     const int q = warp & 3;
+    const int hc = (warp - 2) >> 2;
     const int t128 = q * 32 + lane;
-    int it = 0;
-    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
-      const int a = it & 1, aph = (it >> 1) & 1;
-      mbar_wait(&a_full[a], aph);
-      tc_fence_after();
-      uint32_t r0[32], r1[32];
-      const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + a * 64;
-      tmem_ld_32x32(taddr, r0);
-      tmem_ld_32x32(taddr + 32, r1);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&a_empty[a]);
+    float* my_bnd = sBnd + q * kBndFloats;             // what the warp below me needs: my first four rows
+    const float* next_bnd = sBnd + (q + 1) * kBndFloats;   // q == 3: slot 4 = carry from tile 1
+    int n = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x) {
+#pragma unroll 1
+      for (int tt = 0; tt < 2; ++tt, ++n) {
+        const int tile = 1 - tt;
+        const int a = n & 1, aph = (n >> 1) & 1;
+        mbar_wait(&a_full[a], aph);
+        tc_fence_after();
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + a * 256 + hc * 16;
+        float acc[16];
+        {
+          uint32_t r[16];
+          tmem_ld_32x16(taddr, r);
+          tmem_ld_wait();
 #pragma unroll
-      for (int tile = 0; tile < 2; ++tile) {
+          for (int j = 0; j < 16; ++j) acc[j] = __uint_as_float(r[j]);
+        }
+        uint32_t r[4][16];
+#pragma unroll
+        for (int kw = 1; kw < 5; ++kw) tmem_ld_32x16(taddr + kw * 32, r[kw - 1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_empty[a]);
+#pragma unroll
+        for (int kw = 1; kw < 5; ++kw) {
+          // rows 0..3 of this warp are the rows 32..35 of the warp above it in the tile (for tile 1, warp 0:
+          // of tile 0's last warp, through the carry slot)
+          if (lane < 4) {
+            float* dst = ((tile == 1 && q == 0) ? sBnd + 4 * kBndFloats : my_bnd) + ((kw - 1) * 4 + lane) * 32 + hc * 16;
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              *reinterpret_cast<float4*>(dst + j) =
+                  make_float4(__uint_as_float(r[kw - 1][j]), __uint_as_float(r[kw - 1][j + 1]),
+                              __uint_as_float(r[kw - 1][j + 2]), __uint_as_float(r[kw - 1][j + 3]));
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float v = __shfl_down_sync(0xffffffffu, __uint_as_float(r[kw - 1][j]), kw);
+            if (lane + kw < 32) acc[j] += v;
+          }
+        }
+        epi_bar256();                                  // boundary rows of all warps (and the carry) are in place
+        if (lane >= 28 && !(tile == 1 && q == 3)) {
+          // q == 3 of tile 0 continues into tile 1 (carry slot); tile 1's last rows are beyond the image
+          const float* src = (q == 3) ? sBnd + 4 * kBndFloats : next_bnd;
+#pragma unroll
+          for (int kw = 1; kw < 5; ++kw) {
+            const int l2 = lane + kw - 32;
+            if (l2 >= 0) {
+              const float* p = src + ((kw - 1) * 4 + l2) * 32 + hc * 16;
+#pragma unroll
+              for (int j = 0; j < 16; j += 4) {
+                const float4 v = *reinterpret_cast<const float4*>(p + j);
+                acc[j] += v.x; acc[j + 1] += v.y; acc[j + 2] += v.z; acc[j + 3] += v.w;
+              }
+            }
+          }
+        }
         const int m = tile * 128 + t128;
         const int h = m / PWID, w = m % PWID;
         if (h < HW && w < HW) {
-          uint4* dst = reinterpret_cast<uint4*>(dx + (((size_t)img * HW + h) * HW + w) * CIN);
-          const uint32_t* r = tile == 0 ? r0 : r1;
+          uint4* dst = reinterpret_cast<uint4*>(dx + (((size_t)img * HW + h) * HW + w) * CIN + hc * 16);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
+          for (int j = 0; j < 2; ++j) {
             uint4 pk;
-            pk.x = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-            pk.y = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-            pk.z = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-            pk.w = mtb::pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            pk.x = mtb::pack_bf16x2(acc[8 * j + 0], acc[8 * j + 1]);
+            pk.y = mtb::pack_bf16x2(acc[8 * j + 2], acc[8 * j + 3]);
+            pk.z = mtb::pack_bf16x2(acc[8 * j + 4], acc[8 * j + 5]);
+            pk.w = mtb::pack_bf16x2(acc[8 * j + 6], acc[8 * j + 7]);
             dst[j] = pk;
           }
         }
+        epi_bar256();                                  // boundary buffers free for the next tile
       }
     }
   }
   __syncthreads();
-  if (warp == 1) { tc_fence_after(); tmem_dealloc<128>(tmem); }
+  if (warp == 1) { tc_fence_after(); tmem_dealloc<512>(tmem); }
 }
 
 // ======================================================================================= wgrad
@@ -689,7 +748,7 @@ int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int 
   MTB_REQUIRE(get_map(&md, dy_bf16, B, 1) && get_map(&mw, w_bf16, 0, 3), "conv2_dgrad: tensor map encode failed");
   static bool attr = false;
   if (int e = set_smem(conv2_dgrad_kernel<false>, dg::kSmem, &attr)) return e;
-  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<false>, dim3(grid_for(B)), dim3(kThreads), (size_t)dg::kSmem, stream, md,
+  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<false>, dim3(grid_for(B)), dim3(kThreadsD), (size_t)dg::kSmem, stream, md,
                              mw, reinterpret_cast<bf16*>(dx_bf16), B, PooledGrad{nullptr, nullptr, nullptr}));
   return 0;
 }
@@ -704,7 +763,7 @@ int mtb_conv2_dgrad_unpool(const void* dflat_bf16, const void* pooled_bf16, cons
   static bool attr = false;
   if (int e = set_smem(conv2_dgrad_kernel<true>, dg::kSmem, &attr)) return e;
   const PooledGrad pg{reinterpret_cast<const bf16*>(dflat_bf16), reinterpret_cast<const bf16*>(pooled_bf16), idx};
-  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<true>, dim3(grid_for(B)), dim3(kThreads + kBuilders), (size_t)dg::kSmem,
+  MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<true>, dim3(grid_for(B)), dim3(kThreadsD + kBuildersD), (size_t)dg::kSmem,
                              stream, mw, mw, reinterpret_cast<bf16*>(dx_bf16), B, pg));
   return 0;
 }
