@@ -131,10 +131,13 @@ def stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+_KERNELS_PER_CALL = {"mtb_conv2_wgrad": 2, "mtb_conv2_wgrad_unpool": 2}      # main kernel + partial-sum reduction
+
+
 def call(name: str, *args) -> None:
     """Call ``name(*args, current_stream)`` and raise on a non-zero return."""
     global LAUNCHES
-    LAUNCHES += 1
+    LAUNCHES += _KERNELS_PER_CALL.get(name, 1)
     check(getattr(lib(), name)(*args, stream_ptr()), name)
 
 

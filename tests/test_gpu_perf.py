@@ -1,0 +1,28 @@
+"""Perf-regression tier (SURVEY §4.2 last row): the flagship step must stay well above the
+library baseline measured on the same hardware (0.63 M images/s on one B200)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_bench_contract_and_floor():
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "60", "--warmup", "5"],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300, cwd=ROOT)
+    assert p.returncode == 0, p.stdout[-2000:]
+    line = [l for l in p.stdout.splitlines() if l.startswith("{")][-1]
+    r = json.loads(line)
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "clocks", "gpu_launches", "e2e"):
+        assert k in r, k
+    assert r["n_gpus"] == 1 and r["steps"] == 60 and r["gpu_launches"] > 0
+    assert r["e2e"]["h2d_bytes_per_step"] == 1024 * 784 * 4 + 1024 * 4 and r["e2e"]["d2h_bytes_per_step"] == 4
+    assert r["config"]["loss_last"] < r["config"]["loss_first"]
+    # 4x the library baseline is the floor; the measured value is ~7x
+    assert r["value"] > 2.5e6, r["value"]
+    assert r["e2e"]["value"] > 2.0e6, r["e2e"]
