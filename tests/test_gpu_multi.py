@@ -37,6 +37,20 @@ def test_fused_allreduce_dp_equivalence(tmp_path):
     assert rc == 0 and out.count("GPU_FUSED_OK") == n, out[-4000:]
 
 
+def test_weight_average_mode_on_gpus(tmp_path):
+    n = _world()
+    rc, out = _run(n, "weight_avg", tmp_path)
+    assert rc == 0 and out.count("GPU_WAVG_OK") == n, out[-4000:]
+
+
+def test_dead_rank_gives_clean_failure_on_gpus(tmp_path):
+    """Only 2 ranks: one stalls, the survivor must report a timeout within the spin limit."""
+    rc, out = _run(2, "die", tmp_path, timeout=180)
+    assert rc != 0
+    assert "UNEXPECTED_SUCCESS" not in out, out[-3000:]
+    assert "CLEAN_FAILURE" in out, out[-3000:]
+
+
 def test_trainer_fit_multi_gpu(tmp_path):
     n = _world()
     rc, out = _run(n, "train", tmp_path)

@@ -125,6 +125,54 @@ def train(comm, outdir):
     tr.close()
 
 
+def weight_avg(comm, outdir):
+    """Reference-style sync on GPUs (mpipy.py:95-153 semantics, fixed so every rank gets the mean):
+    local momentum-SGD steps, parameters averaged every 5 steps through the P2P allreduce."""
+    cfg = TrainConfig(model="tutorial512", batch=32, max_steps=12, eval_every=0, log_every=0, dropout=False,
+                      sync="weight_avg", sync_period=5, sync_include_bias=True)
+    tr = Trainer(cfg, comm)
+    tr.load_data(shards_for(comm.rank, 256))
+    for _ in range(11):                                      # steps 0..10: syncs after steps 5 and 10
+        tr.step()
+    tr.engine.synchronize()
+    mine = tr.engine.flat_params.clone()
+    ref = mine.clone()
+    comm.bcast(ref, root=0)
+    assert torch.equal(mine, ref), "weight_avg: replicas differ right after a sync step"
+    tr.step()                                                # one local step on different data: replicas drift apart
+    drift = tr.engine.flat_params.clone()
+    ref2 = drift.clone()
+    comm.bcast(ref2, root=0)
+    if comm.rank != 0:
+        assert not torch.equal(drift, ref2), "weight_avg: local step did not change the replica"
+    print(f"GPU_WAVG_OK rank {comm.rank}/{comm.size}", flush=True)
+    tr.close()
+
+
+def die(comm, outdir):
+    """Fault tier on GPUs: rank 1 stalls (a wedged process, not a dead one: the launcher would end the
+    job by itself for an exit) and never reaches the collective; rank 0 must come back with a clear
+    error (device-side spin limit -> status word -> CommTimeout), not hang with the GPU spinning."""
+    import time
+    cfg = TrainConfig(model="tutorial512", batch=32, eval_every=0, log_every=0, dropout=False, cuda_graph=False)
+    tr = Trainer(cfg, comm)
+    tr.load_data(shards_for(comm.rank, 128))
+    tr.step()
+    if comm.rank == 1:
+        time.sleep(150)
+        os._exit(17)
+    t0 = time.time()
+    try:
+        tr.step()
+        tr.engine.synchronize()
+        comm.check_status()
+    except Exception as e:  # noqa: BLE001
+        print(f"CLEAN_FAILURE {type(e).__name__} after {time.time() - t0:.1f}s", flush=True)
+        os._exit(3)
+    print("UNEXPECTED_SUCCESS", flush=True)
+    os._exit(0)
+
+
 def main():
     mode, outdir = sys.argv[1], sys.argv[2]
     comm = world.init("p2p", "cuda", timeout_s=60)
@@ -134,6 +182,10 @@ def main():
         fused(comm, outdir)
     elif mode == "train":
         train(comm, outdir)
+    elif mode == "weight_avg":
+        weight_avg(comm, outdir)
+    elif mode == "die":
+        die(comm, outdir)
     world.finalize()
 
 
