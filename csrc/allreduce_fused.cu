@@ -58,6 +58,8 @@ struct FusedParams {
   float momentum, beta1, beta2, eps, wd;
   int n_ranges;
   long long range_begin[kMaxRanges], range_end[kMaxRanges];   // where the L2 term applies
+  int n_sharded;                                    // ranges whose fp32 master stays with the slice owner
+  long long shard_begin[4], shard_end[4];
   long long* advance_step;                          // bumped by the last block to finish (may be null)
   unsigned int* done_counter;
 };
@@ -146,6 +148,14 @@ __device__ __forceinline__ bool decays(const FusedParams& p, long long i) {
   return d;
 }
 
+__device__ __forceinline__ bool master_sharded(const FusedParams& p, long long i) {
+  bool s = false;
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+    if (r < p.n_sharded && i >= p.shard_begin[r] && i < p.shard_end[r]) s = true;
+  return s;
+}
+
 // One float4 of the optimizer.  g is the already averaged gradient.
 __device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g) {
   float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
@@ -222,11 +232,14 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
         *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
         if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = wb;
       } else if (KIND == kNvls) {
-        multimem_st_f4(p.mc_params + i, w);
+        // sharded master: my fp32 copy is the only current one, peers get the bf16 shadow
+        if (master_sharded(p, i)) *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
+        else multimem_st_f4(p.mc_params + i, w);
         if (p.mc_shadow) multimem_st_bf16x4(p.mc_shadow + i, wb);
       } else {
+        const bool sharded = master_sharded(p, i);
         for (int r = 0; r < p.world; ++r) {
-          *reinterpret_cast<float4*>(p.params[r] + i) = w;
+          if (!sharded || r == p.rank) *reinterpret_cast<float4*>(p.params[r] + i) = w;
           if (p.shadow[r]) *reinterpret_cast<uint2*>(p.shadow[r] + i) = wb;
         }
       }
@@ -316,6 +329,10 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->momentum = a->momentum; p->beta1 = a->beta1; p->beta2 = a->beta2; p->eps = a->eps; p->wd = a->wd;
   p->n_ranges = a->n_ranges;
   for (int r = 0; r < kMaxRanges; ++r) { p->range_begin[r] = a->range_begin[r]; p->range_end[r] = a->range_end[r]; }
+  MTB_REQUIRE(a->n_sharded >= 0 && a->n_sharded <= 4, "fused: at most 4 sharded-master ranges");
+  p->n_sharded = a->n_sharded;
+  for (int r = 0; r < 4; ++r) { p->shard_begin[r] = a->shard_begin[r]; p->shard_end[r] = a->shard_end[r]; }
+  MTB_REQUIRE(p->n_sharded == 0 || (a->shadow[a->rank] != nullptr), "fused: sharded masters need the bf16 shadow");
   p->advance_step = reinterpret_cast<long long*>(a->advance_step);
   p->done_counter = reinterpret_cast<unsigned int*>(a->done_counter);
   MTB_REQUIRE(p->advance_step == nullptr || p->done_counter != nullptr, "fused: advance_step needs done_counter");

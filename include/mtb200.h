@@ -166,6 +166,11 @@ typedef struct mtb_fused_args {
   int n_ranges;
   long long range_begin[8], range_end[8];
   int grid, block;
+  /* Sharded fp32 master (two-shot / nvls only): inside these element ranges the owner of a slice keeps the only
+   * up-to-date fp32 copy and broadcasts just the bf16 shadow, 2 instead of 6 bytes per parameter over NVLink.
+   * Use it for tensors whose consumers read the shadow (the big GEMM / convolution weights). */
+  int n_sharded;
+  long long shard_begin[4], shard_end[4];
   void* advance_step;   /* if set: *advance_step += 1 once every block of this launch has finished (global_step=iter_, mpipy.py:66) */
   void* done_counter;   /* 32-bit scratch for that, zero between launches */
 } mtb_fused_args;

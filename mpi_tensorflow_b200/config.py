@@ -47,6 +47,8 @@ class TrainConfig:
     sync_root_only: bool = False        # True reproduces mpipy.py:129 (mean stays on root)
     comm_algo: str = "auto"             # auto | oneshot | twoshot | nvls | nccl (baseline)
     comm_dtype: str = "fp32"            # gradient wire format: fp32 | bf16
+    shard_master: bool = True           # two-shot / nvls: the big weights' fp32 master stays with the slice owner,
+                                        # only their bf16 shadow is broadcast (gathered on demand for checkpoints)
     backend: str = "auto"               # auto | p2p | nccl | gloo | shm | self
     device: str = "auto"                # auto | cuda | cpu
     overlap: bool = False               # fc-bucket allreduce+update on a comm stream under the conv backward

@@ -95,6 +95,8 @@ class NativeEngine:
         self.loss_acc = torch.zeros(1, device=dev)
         self.err_acc = torch.zeros(1, dtype=torch.int32, device=dev)
         self._zero_args = None
+        self._masters_dirty = self._slots_dirty = False
+        self._shard_master = bool(self.cfg.shard_master) and self.p2p is not None and self.world > 1
         self._done = torch.zeros(1, dtype=torch.int32, device=dev)
         self._seq = torch.zeros(N.lib().mtb_fused_max_blocks(), dtype=torch.int32, device=dev)
         self._status = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -163,6 +165,44 @@ class NativeEngine:
 
     def synchronize(self):
         torch.cuda.current_stream().synchronize()
+
+    # -- state that the two-shot / nvls update keeps only with the owner of each slice ------------
+    def _owned(self):
+        """Element range [lo, hi) of the flat buffers this rank owns in a whole-buffer K1 launch."""
+        vecs = self.n // 4
+        per = (vecs + self.world - 1) // self.world
+        lo = min(per * self.p2p.rank, vecs) * 4
+        return lo, min(lo + per * 4, self.n)
+
+    def _gather_owned(self, buf: torch.Tensor, ranges):
+        """Make ``buf`` complete on every rank: each rank contributes its owned part of every range
+        (zero elsewhere) and the parts are summed.  Collective; used at checkpoint / inspection time."""
+        olo, ohi = self._owned()
+        for lo, hi in ranges:
+            seg = torch.zeros(hi - lo, device=self.device)
+            a, b = max(lo, olo), min(hi, ohi)
+            if b > a:
+                seg[a - lo:b - lo] = buf[a:b]
+            self.p2p.allreduce(seg, average=False)
+            buf[lo:hi] = seg
+
+    def sync_state(self):
+        """COLLECTIVE.  After sharded-master / sharded-slot updates, complete the fp32 master weights
+        and the optimizer slots on every rank (no-op otherwise).  Call on all ranks before
+        ``get_params`` / ``get_slots`` are used on any of them."""
+        if self.p2p is None or self.world == 1:
+            return
+        self.synchronize()
+        flags = self.p2p.boot.allgather_object((self._masters_dirty, self._slots_dirty))
+        if any(f[0] for f in flags):
+            big = [self.spec.param("conv2_weight"), self.spec.param("fc1_weight")]
+            self._gather_owned(self.flat_params, [(p.offset, p.offset + p.numel) for p in big])
+            self._masters_dirty = False
+        if any(f[1] for f in flags):
+            for sl in self.slots:
+                self._gather_owned(sl, [(0, self.n)])
+            self._slots_dirty = False
+        self.synchronize()
 
     def get_params(self):
         self.synchronize()
@@ -377,6 +417,11 @@ class NativeEngine:
         a.n_ranges = len(dec) if c.weight_decay else 0
         for i, p in enumerate(dec):
             a.range_begin[i], a.range_end[i] = p.offset, p.offset + p.numel
+        if peers and self._shard_master:
+            big = [s.param("conv2_weight"), s.param("fc1_weight")]
+            a.n_sharded = len(big)
+            for i, p in enumerate(big):
+                a.shard_begin[i], a.shard_end[i] = p.offset, p.offset + p.numel
         return a
 
     def _pick_algo(self, count: int) -> int:
@@ -403,6 +448,11 @@ class NativeEngine:
         a = self._fused_args(peers, lr_override)
         a.offset, a.count = lo, hi - lo
         a.algo = self._pick_algo(hi - lo) if peers else 0
+        if a.algo == 0:
+            a.n_sharded = 0                                            # one-shot: every rank computes everything
+        elif peers and self.world > 1:
+            self._masters_dirty = self._masters_dirty or a.n_sharded > 0
+            self._slots_dirty = True                                   # slots of non-owned slices are not maintained
         a.grid = grid
         if advance:                                                     # iter_ += 1 in the same launch
             a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done.data_ptr()

@@ -31,6 +31,7 @@ class FusedArgs(C.Structure):
         ("momentum", f32), ("beta1", f32), ("beta2", f32), ("eps", f32), ("wd", f32),
         ("n_ranges", i32), ("range_begin", i64 * 8), ("range_end", i64 * 8),
         ("grid", i32), ("block", i32),
+        ("n_sharded", i32), ("shard_begin", i64 * 4), ("shard_end", i64 * 4),
         ("advance_step", vp), ("done_counter", vp),
     ]
 

@@ -254,6 +254,8 @@ class Trainer:
     def save_checkpoint(self, path: str) -> None:
         """Rank 0 writes; everyone waits.  Names/layouts per SURVEY §5.4."""
         c = self.cfg
+        if hasattr(self.engine, "sync_state"):
+            self.engine.sync_state()               # collective: masters / slots kept by slice owners are gathered
         if self.comm.rank == 0:
             named = ckpt.to_named(self.spec, self.engine.get_params(), self.engine.get_slots(),
                                   self.global_step, c.optimizer, c.checkpoint_names, c.beta1, c.beta2)

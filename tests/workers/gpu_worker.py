@@ -80,6 +80,7 @@ def fused(comm, outdir):
             losses.append(tr.step(torch.from_numpy(gx[lo:lo + b]), torch.from_numpy(gy[lo:lo + b]).int()))
         tr.engine.synchronize()
         comm.check_status()
+        tr.engine.sync_state()                   # fp32 masters of the big weights live with their slice owners
         mine = tr.engine.flat_params.clone()
         ref = mine.clone()
         comm.bcast(ref, root=0)
@@ -114,6 +115,7 @@ def train(comm, outdir):
     tr = Trainer(cfg, comm)
     tr.load_data()
     res = tr.fit()
+    tr.engine.sync_state()
     mine = tr.engine.flat_params.clone()
     ref = mine.clone()
     comm.bcast(ref, root=0)
