@@ -388,9 +388,9 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
           kq[k] = __ldg(reinterpret_cast<const uint2*>(idx + o));
         }
       }
+      load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);   // xs is this group's own: free since the last bar
       mbar_wait(&x_empty[g], ph ^ 1);
       if (t == 0) TRACE(16 + it, 5);
-      load_xs<kProducers>(xs, x + (size_t)img * IMG * IMG, t);
       if (t == 0) TRACE(16 + it, 6);
       // dA rows of one pooling window: gradient goes to the argmax position if the pooled
       // activation is positive (ReLU), the other three positions get zero
@@ -430,12 +430,13 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
       uint32_t r[32];
       tmem_ld_32x32(tmem + ((uint32_t)(q * 32) << 16), r);
       tmem_ld_wait();
-      if (kw < 5 && kh < 5) {
+      float* dst = (kw < 5 && kh < 5) ? dW + (kh * 5 + kw) * C1 : ((kw == 0 && kh == 5) ? db : nullptr);
+      if (dst != nullptr) {
 #pragma unroll
-        for (int c = 0; c < 32; ++c) atomicAdd(dW + (kh * 5 + kw) * C1 + c, __uint_as_float(r[c]));
-      } else if (kw == 0 && kh == 5) {
-#pragma unroll
-        for (int c = 0; c < 32; ++c) atomicAdd(db + c, __uint_as_float(r[c]));
+        for (int c = 0; c < 32; c += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c), "f"(__uint_as_float(r[c])),
+                       "f"(__uint_as_float(r[c + 1])), "f"(__uint_as_float(r[c + 2])), "f"(__uint_as_float(r[c + 3]))
+                       : "memory");
       }
       tc_fence_before();
       if (L == 0) TRACE(30, 4);
