@@ -46,7 +46,7 @@ struct GemmParams {
 
 template <int BN>
 struct Cfg {
-  static constexpr int kStages = BN == 128 ? 4 : 6;
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 4 : 6);      // 256: 4 x 48 KB
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kSmemBytes = 1024 + kStages * (kABytes + kBBytes) + 256;
@@ -341,13 +341,13 @@ extern "C" {
 
 size_t mtb_gemm_workspace_bytes(int M, int N, int bn, int splits) {
   if (splits <= 1) return 0;
-  if (bn != 64 && bn != 128) bn = 128;
+  if (bn != 64 && bn != 128 && bn != 256) bn = 128;
   size_t tiles = (size_t)mtb::ceil_div(M, BM) * (size_t)mtb::ceil_div(N, bn);
   return tiles * (size_t)splits * BM * bn * sizeof(float);
 }
 
 size_t mtb_gemm_counter_bytes(int M, int N, int bn) {
-  if (bn != 64 && bn != 128) bn = 128;
+  if (bn != 64 && bn != 128 && bn != 256) bn = 128;
   return (size_t)mtb::ceil_div(M, BM) * (size_t)mtb::ceil_div(N, bn) * sizeof(unsigned int);
 }
 
@@ -358,7 +358,7 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm: null pointer or empty shape");
   MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm: operand row pitch must be a multiple of 16 bytes");
   MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: operands must be 16-byte aligned");
-  if (bn != 64 && bn != 128) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
+  if (bn != 64 && bn != 128 && bn != 256) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
   if (splits < 1) splits = 1;
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
@@ -408,6 +408,8 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)
   MTB_GEMM_CASE(128, true, true) MTB_GEMM_CASE(64, false, false) MTB_GEMM_CASE(64, false, true)
   MTB_GEMM_CASE(64, true, false) MTB_GEMM_CASE(64, true, true)
+  MTB_GEMM_CASE(256, false, false) MTB_GEMM_CASE(256, false, true) MTB_GEMM_CASE(256, true, false)
+  MTB_GEMM_CASE(256, true, true)
 #undef MTB_GEMM_CASE
   return mtb_set_error_msg(MTB_E_ARG, "gemm: no kernel variant", __FILE__, __LINE__);
 }

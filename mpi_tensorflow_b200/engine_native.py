@@ -335,9 +335,11 @@ class NativeEngine:
             N.call("mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
         # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand.  Runs BEFORE the
         # weight gradient so that the last reader of the FC1 weights is done when the bucket closes.
-        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=128)
+        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False,
+                    bn=256 if B >= 512 else 128)
         # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket
-        N.gemm_bf16(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=128)
+        N.gemm_bf16(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True,
+                    bn=256 if s.fc % 256 == 0 else 128)
 
     def _backward_conv(self, B: int):
         s = self.spec

@@ -50,6 +50,8 @@ GEMM_SHAPES = [
     (800, 64, 19600, 64, 16),        # conv2 wgrad, split-K
     (19600, 800, 64, 128, 1),        # conv2 dgrad
     (300, 200, 136, 64, 3),          # ragged everything + split-K
+    (1024, 3136, 1024, 256, 1),      # wide tile (BN = 256): fc1 dgrad shape
+    (3136, 1024, 200, 256, 1),       # wide tile, ragged K
 ]
 
 
