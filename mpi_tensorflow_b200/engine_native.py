@@ -95,6 +95,7 @@ class NativeEngine:
         self.loss_acc = torch.zeros(1, device=dev)
         self.err_acc = torch.zeros(1, dtype=torch.int32, device=dev)
         self._zero_args = None
+        self._scratch = {}
         self._masters_dirty = self._slots_dirty = False
         self._shard_master = bool(self.cfg.shard_master) and self.p2p is not None and self.world > 1
         self._done = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -296,9 +297,16 @@ class NativeEngine:
                    s.c2)
         # FC1 + bias + ReLU + dropout in the GEMM epilogue (mpipy.py:165-166)
         flat = self.a2p.view(self.Bmax, s.flat_dim)
+        bn, splits = 64 if B * s.fc < 96 * 128 * 128 else 128, 1
+        tiles = -(-B // 128) * -(-s.fc // bn)
+        if tiles < 64 and os.environ.get("MTB_FC_SPLITK") == "1":
+            # small batch: split K so the GEMM covers the chip.  Measured slower at batch 100 (the
+            # last-arriver reduction costs more than the idle SMs), so opt-in only.
+            splits = max(1, min(8, 128 // tiles))
+        ws, cnt = self._splitk_scratch("fc1_fprop", B, s.fc, bn, splits)
         N.gemm_bf16(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
-                    keep_prob=keep, seed=c.seed, step_ptr=self.dev_step,
-                    bn=int(os.environ.get("MTB_FC1_BN", "0")) or (64 if B * s.fc < 96 * 128 * 128 else 128))
+                    keep_prob=keep, seed=c.seed, step_ptr=self.dev_step, bn=bn, splits=splits, workspace=ws,
+                    counters=cnt)
         # FC2 + softmax + CE + dlogits (mpipy.py:167, :55-56, :67)
         head = (self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
                 wy if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
@@ -335,11 +343,16 @@ class NativeEngine:
             N.call("mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
         # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand.  Runs BEFORE the
         # weight gradient so that the last reader of the FC1 weights is done when the bucket closes.
-        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False,
-                    bn=256 if B >= 512 else 128)
-        # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket
+        bn = 256 if B >= 512 else 128
+        tiles = -(-B // 128) * -(-s.flat_dim // bn)
+        splits = max(1, min(4, 128 // tiles)) if (tiles < 64 and os.environ.get("MTB_FC_SPLITK") == "1") else 1
+        ws, cnt = self._splitk_scratch("fc1_dgrad", B, s.flat_dim, bn, splits)
+        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=bn, splits=splits,
+                    workspace=ws, counters=cnt)
+        # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket (K = batch: wide tiles
+        # only pay off when K is long enough to amortise their epilogue)
         N.gemm_bf16(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True,
-                    bn=256 if s.fc % 256 == 0 else 128)
+                    bn=256 if (s.fc % 256 == 0 and B >= 512) else 128)
 
     def _backward_conv(self, B: int):
         s = self.spec
@@ -373,6 +386,17 @@ class NativeEngine:
         else:
             N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
                    self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
+
+    def _splitk_scratch(self, key: str, M: int, Nn: int, bn: int, splits: int):
+        """Workspace and tile counters of a split-K GEMM, allocated once per call site and shape."""
+        if splits <= 1:
+            return None, None
+        k = (key, M, Nn, bn, splits)
+        if k not in self._scratch:
+            ws, cn = N.gemm_scratch_sizes(M, Nn, bn, splits)
+            self._scratch[k] = (torch.zeros(max(ws, 16), dtype=torch.uint8, device=self.device),
+                                torch.zeros(max(cn, 16), dtype=torch.uint8, device=self.device))
+        return self._scratch[k]
 
     def _zero_list(self):
         if self._zero_args is None:
