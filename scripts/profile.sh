@@ -16,4 +16,4 @@ else
   timeout 700 ncu --set full --clock-control none --import-source on -k "regex:${2:-conv}" -s 12 -c 12 \
     -o gpurun_out/prof $cmd > gpurun_out/ncu_full.log 2>&1
 fi
-tail -2 gpurun_out/ncu*.log
+for f in gpurun_out/ncu*.log; do tail -n 2 "$f"; done
