@@ -18,7 +18,8 @@ from typing import Optional
 class TrainConfig:
     # model
     model: str = "tutorial512"          # tutorial512 | official1024 | wide
-    dtype: str = "bf16"                 # compute dtype on GPU: bf16 | fp32 (TF32 MMA)
+    dtype: str = "bf16"                 # GPU compute: bf16 tensor-core operands, fp32 accumulate / master / optimizer.
+                                        # "fp32" is accepted for the CPU engine; the GPU engine warns and runs bf16.
     seed: int = 1                       # mpipy.py:40
     # data
     data: str = "synthetic"             # synthetic | mnist
@@ -46,7 +47,7 @@ class TrainConfig:
     sync_include_momentum: bool = False
     sync_root_only: bool = False        # True reproduces mpipy.py:129 (mean stays on root)
     comm_algo: str = "auto"             # auto | oneshot | twoshot | nvls | nccl (baseline)
-    comm_dtype: str = "fp32"            # gradient wire format: fp32 | bf16
+    comm_dtype: str = "fp32"            # gradient wire format; only fp32 is implemented (bf16 is rejected)
     shard_master: bool = True           # two-shot / nvls: the big weights' fp32 master stays with the slice owner,
                                         # only their bf16 shadow is broadcast (gathered on demand for checkpoints)
     backend: str = "auto"               # auto | p2p | nccl | gloo | shm | self

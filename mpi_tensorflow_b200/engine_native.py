@@ -39,6 +39,12 @@ class NativeEngine:
         if device.type != "cuda":
             raise RuntimeError("NativeEngine needs a CUDA device")
         N.lib()                                   # fail loudly if the extension is missing
+        if cfg.comm_dtype != "fp32":
+            raise NotImplementedError("comm_dtype='bf16' is not implemented: gradients cross NVLink in fp32")
+        if cfg.dtype == "fp32":
+            import warnings
+            warnings.warn("the GPU engine has no fp32/TF32 compute path: running bf16 tensor-core operands with fp32 "
+                          "accumulation, fp32 master weights and fp32 optimizer state", stacklevel=2)
         self.spec, self.cfg, self.comm, self.device = spec, cfg, comm, device
         torch.cuda.set_device(device)
         self.B = cfg.batch
