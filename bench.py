@@ -232,8 +232,9 @@ def run_ours(args) -> dict:
         ms3 = timed_region(comm, loop3)
         e2e = {"value": n * B * K / (ms2 / 1e3), "unit": "images/s", "ms_per_step": ms2 / K,
                "api": "Trainer.fit_stream(host_images, host_labels, steps)",
-               "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 4,
-               "losses_read": len(got["losses"]),
+               "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 8,
+               "d2h_how": "the update kernel stores {step, loss} (8 B) into a pinned host ring; the host polls it",
+               "losses_read": len(got["losses"]), "loss_last": got["losses"][-1],
                "sync_step_api": {"api": "Trainer.step(images, labels)", "value": n * B * K / (ms3 / 1e3),
                                  "ms_per_step": ms3 / K}}
 

@@ -62,6 +62,9 @@ struct FusedParams {
   long long shard_begin[4], shard_end[4];
   long long* advance_step;                          // bumped by the last block to finish (may be null)
   unsigned int* done_counter;
+  const float* loss_src;                            // step result mailed to the host by the last block (may be null)
+  unsigned long long* loss_mail;                    // pinned host ring of {f32 loss, u32 step} words
+  int loss_ring;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -282,7 +285,15 @@ fused_allreduce_update_kernel(const FusedParams p) {
       __threadfence();
       if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
         *p.done_counter = 0u;
-        *p.advance_step += 1;
+        const long long next = *p.advance_step + 1;
+        *p.advance_step = next;
+        if (p.loss_mail != nullptr) {
+          // one 8-byte store = one PCIe write: the host sees the loss and its step number together
+          const unsigned long long word = (static_cast<unsigned long long>(static_cast<uint32_t>(next)) << 32) |
+                                          __float_as_uint(*p.loss_src);
+          asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.loss_mail + ((next - 1) & (p.loss_ring - 1))),
+                       "l"(word) : "memory");
+        }
       }
     }
   }
@@ -336,6 +347,12 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->advance_step = reinterpret_cast<long long*>(a->advance_step);
   p->done_counter = reinterpret_cast<unsigned int*>(a->done_counter);
   MTB_REQUIRE(p->advance_step == nullptr || p->done_counter != nullptr, "fused: advance_step needs done_counter");
+  p->loss_src = reinterpret_cast<const float*>(a->loss_src);
+  p->loss_mail = reinterpret_cast<unsigned long long*>(a->loss_mail);
+  p->loss_ring = a->loss_ring;
+  MTB_REQUIRE(p->loss_mail == nullptr || (p->advance_step != nullptr && p->loss_src != nullptr && p->loss_ring > 0 &&
+                                          (p->loss_ring & (p->loss_ring - 1)) == 0),
+              "fused: loss_mail needs advance_step, loss_src and a power-of-two loss_ring");
   return 0;
 }
 

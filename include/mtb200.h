@@ -173,6 +173,12 @@ typedef struct mtb_fused_args {
   long long shard_begin[4], shard_end[4];
   void* advance_step;   /* if set: *advance_step += 1 once every block of this launch has finished (global_step=iter_, mpipy.py:66) */
   void* done_counter;   /* 32-bit scratch for that, zero between launches */
+  /* Loss mailbox (needs advance_step): the block that bumps the step also stores {u32 new step : f32 *loss_src} as one
+   * 8-byte word into loss_mail[(new step - 1) % loss_ring], a ring in pinned (device-visible) host memory, so the host
+   * reads every step's loss (the fetch of sess.run([optimizer, loss]), mpipy.py:83-85) without a copy or a sync. */
+  const void* loss_src;
+  void* loss_mail;
+  int loss_ring;        /* power of two */
 } mtb_fused_args;
 int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
 int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */

@@ -18,6 +18,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import time
 from typing import Dict, List, Optional
 
 import numpy as np
@@ -105,6 +106,9 @@ class NativeEngine:
         self._masters_dirty = self._slots_dirty = False
         self._shard_master = bool(self.cfg.shard_master) and self.p2p is not None and self.world > 1
         self._done = torch.zeros(1, dtype=torch.int32, device=dev)
+        # loss mailbox: K1's last block stores {step, loss} words straight into this pinned host ring
+        self._mail = torch.zeros(self._MAIL_RING, dtype=torch.int64).pin_memory()
+        self._mail_np = self._mail.numpy()
         self._seq = torch.zeros(N.lib().mtb_fused_max_blocks(), dtype=torch.int32, device=dev)
         self._status = torch.zeros(1, dtype=torch.int32, device=dev)
         self.P = {p.key: self.flat_params[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
@@ -137,6 +141,7 @@ class NativeEngine:
         # batch window fused into the kernels that read the batch (needs both fast paths)
         self._can_window = self.conv1_tc and self._fast_head
         self._windowed = False
+        self._stream_buf = None
         # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
         want = self.conv_impl
         have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2))
@@ -271,6 +276,9 @@ class NativeEngine:
         staged batch with a null step pointer."""
         if self._windowed:
             return self.data_x.data_ptr(), self.data_y.data_ptr(), self.dev_step.data_ptr(), self.rows
+        if self._stream_buf is not None:         # host-streamed training: read the half of the double buffer directly
+            st = self._stream_state
+            return st["x"][self._stream_buf].data_ptr(), st["y"][self._stream_buf].data_ptr(), None, 0
         return self.x_in.data_ptr(), self.y_in.data_ptr(), None, 0
 
     def _forward(self, B: int, train: bool, with_loss: bool, zero: bool = False):
@@ -488,6 +496,7 @@ class NativeEngine:
         a.grid = grid
         if advance:                                                     # iter_ += 1 in the same launch
             a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done.data_ptr()
+            a.loss_src, a.loss_mail, a.loss_ring = self.loss_acc.data_ptr(), self._mail.data_ptr(), self._MAIL_RING
         N.call("mtb_fused_allreduce_update", C.byref(a))
 
     # ------------------------------------------------------------------ engine interface
@@ -498,6 +507,7 @@ class NativeEngine:
         else:
             self._window()
         self._windowed = False
+        self._stream_buf = None
         self._zero_step_accumulators()
         self._forward(self.B, True, True)
         self._backward(self.B)
@@ -522,6 +532,24 @@ class NativeEngine:
                     N.call("mtb_l2_half_sumsq", self.P[p.key].data_ptr(), p.numel, l2.data_ptr())
             loss += self.cfg.weight_decay * float(l2.item())
         return loss
+
+    _MAIL_RING = 16
+
+    def _await_loss(self, step_no: int, timeout: float = 60.0) -> float:
+        """Loss of optimizer step ``step_no`` (1-based value of the device counter after it), read
+        from the pinned mailbox K1 writes: no copy, no stream synchronize, just a poll."""
+        slot, want = (step_no - 1) % self._MAIL_RING, step_no & 0xFFFFFFFF
+        mail, t0, spins = self._mail_np, None, 0
+        while True:
+            word = int(mail[slot])
+            if (word >> 32) & 0xFFFFFFFF == want:
+                return float(np.uint32(word & 0xFFFFFFFF).view(np.float32))
+            spins += 1
+            if spins & 1023 == 0:
+                now = time.monotonic()
+                t0 = now if t0 is None else t0
+                if now - t0 > timeout:
+                    raise RuntimeError(f"step {step_no}: no loss arrived from the device within {timeout:.0f}s")
 
     def _step_body(self):
         if self.conv1_tc:
@@ -564,10 +592,11 @@ class NativeEngine:
             mode = "staged"
         self._run_step(mode)
         self.opt_step += 1
-        return float(self.loss_acc.item()) if read_loss else 0.0
+        return self._await_loss(self.opt_step) if read_loss else 0.0
 
     def _run_step(self, mode: str):
         self._windowed = mode == "window"
+        self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
         if self.cfg.cuda_graph:
             if mode not in self._graphs:
                 self._capture(mode)
@@ -600,21 +629,18 @@ class NativeEngine:
                 ready=[torch.cuda.Event() for _ in range(2)],
                 consumed=[torch.cuda.Event() for _ in range(2)],
                 copy=torch.cuda.Stream(device=dev),
-                loss=torch.zeros(ring, dtype=torch.float32).pin_memory(),
-                loss_ev=[torch.cuda.Event() for _ in range(ring)],
             )
         st = self._stream_state
-        ring = st["loss"].numel()
+        ring = max(1, min(ring, self._MAIL_RING - 1))
         main = torch.cuda.current_stream()
         copy = st["copy"]
         for ev in st["consumed"]:
             ev.record(main)
-        if self.cfg.cuda_graph and "staged" not in self._graphs:
-            self._windowed = False
-            self._capture("staged")
+        direct = self._can_window                  # the kernels that read the batch take any pointer
         losses: List[float] = []
+        first = self.opt_step + 1
         for i in range(steps):
-            k, r = i & 1, i % ring
+            k = i & 1
             o = (i % nwin) * B
             copy.wait_event(st["consumed"][k])                 # the step that used this half has copied it out
             with torch.cuda.stream(copy):
@@ -622,20 +648,18 @@ class NativeEngine:
                 st["y"][k].copy_(hy[o:o + B], non_blocking=True)
                 st["ready"][k].record(copy)
             main.wait_event(st["ready"][k])
-            self.x_in[:B].copy_(st["x"][k], non_blocking=True)
-            self.y_in[:B].copy_(st["y"][k], non_blocking=True)
+            if direct:                                         # one graph per half: no device-to-device copy
+                self._run_step(f"stream{k}")
+            else:
+                self.x_in[:B].copy_(st["x"][k], non_blocking=True)
+                self.y_in[:B].copy_(st["y"][k], non_blocking=True)
+                self._run_step("staged")
             st["consumed"][k].record(main)
-            self._run_step("staged")
-            if i >= ring:                                      # oldest slot of the ring: read it before reuse
-                st["loss_ev"][r].synchronize()
-                losses.append(float(st["loss"][r]))
-            st["loss"][r:r + 1].copy_(self.loss_acc, non_blocking=True)
-            st["loss_ev"][r].record(main)
             self.opt_step += 1
-        for i in range(max(0, steps - ring), steps):
-            r = i % ring
-            st["loss_ev"][r].synchronize()
-            losses.append(float(st["loss"][r]))
+            if i >= ring:                                      # the device mailed it `ring` steps ago
+                losses.append(self._await_loss(first + len(losses)))
+        while len(losses) < steps:
+            losses.append(self._await_loss(first + len(losses)))
         return losses
 
     def _capture(self, mode: str = "staged"):
@@ -643,6 +667,7 @@ class NativeEngine:
         One graph per input mode: ``staged`` reads the batch buffers, ``window`` gathers the
         resident shard's window inside the kernels."""
         self._windowed = mode == "window"
+        self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
         snap = [t.clone() for t in (self.flat_params, self.shadow, self.dev_step, *self.slots)]
         if self.p2p is not None:
             self.p2p.barrier()
@@ -653,6 +678,7 @@ class NativeEngine:
         for t, s in zip((self.flat_params, self.shadow, self.dev_step, *self.slots), snap):
             t.copy_(s)
         torch.cuda.synchronize()
+        self._mail[self.opt_step % self._MAIL_RING] = 0        # the rolled-back warm-up step mailed a loss too
         if self.p2p is not None:
             self.p2p.barrier()
         g = torch.cuda.CUDAGraph()
@@ -673,6 +699,7 @@ class NativeEngine:
             raise ValueError(f"batch {B} exceeds the engine's static capacity {self.Bmax}")
         self.x_in[:B].copy_(x.reshape(B, -1), non_blocking=True)
         self._windowed = False
+        self._stream_buf = None
         self._forward(B, dropout_step is not None, False)
         return self.probs[:B].clone()
 

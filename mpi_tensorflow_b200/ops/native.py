@@ -33,6 +33,7 @@ class FusedArgs(C.Structure):
         ("grid", i32), ("block", i32),
         ("n_sharded", i32), ("shard_begin", i64 * 4), ("shard_end", i64 * 4),
         ("advance_step", vp), ("done_counter", vp),
+        ("loss_src", vp), ("loss_mail", vp), ("loss_ring", i32),
     ]
 
 

@@ -122,3 +122,18 @@ def test_fit_stream_matches_stepwise_training():
     assert np.allclose(la[:3], lb[:3], rtol=5e-3, atol=5e-3)
     assert abs(np.mean(la[-5:]) - np.mean(lb[-5:])) < 0.3 * max(np.mean(lb[-5:]), 0.1)
     assert la[-1] < la[0] and lb[-1] < lb[0]
+
+
+def test_loss_mailbox_matches_device_accumulator():
+    """The loss the update kernel mails into pinned host memory is the device accumulator's
+    value for exactly that step (step number and value travel in one 8-byte store)."""
+    tr = Trainer(_cfg(batch=64), device=torch.device("cuda", 0))
+    tr.load_data(_shards(256))
+    eng = tr.engine
+    for i in range(1, 20):                       # more steps than ring slots: slots are reused
+        mailed = tr.step()
+        torch.cuda.synchronize()
+        assert eng.opt_step == i and int(eng.dev_step.item()) == i
+        assert mailed == pytest.approx(float(eng.loss_acc.item()), rel=0, abs=0)
+    with pytest.raises(RuntimeError):
+        eng._await_loss(eng.opt_step + 1, timeout=0.2)      # a step that never ran
