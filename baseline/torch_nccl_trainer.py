@@ -45,8 +45,9 @@ PRESETS = {"tutorial512": (32, 64, 512, 0.5), "official1024": (32, 64, 1024, 0.6
 
 
 class Step:
-    def __init__(self, model, batch, rows, world, dev, optimizer="momentum", graph=True, seed=1):
+    def __init__(self, model, batch, rows, world, dev, optimizer="momentum", graph=True, seed=1, dtype="bf16"):
         torch.manual_seed(seed)
+        self.bf16 = dtype != "fp32"
         c1, c2, fc, keep = PRESETS[model]
         self.net = MnistCnn(c1, c2, fc, keep).to(dev)
         if os.environ.get("BASELINE_CHANNELS_LAST", "1") == "1":
@@ -88,7 +89,8 @@ class Step:
         self.step_no += 1
 
     def _body(self):
-        with torch.autocast("cuda", dtype=torch.bfloat16):
+        # bf16 arm: autocast; fp32 arm: fp32 tensors with TF32 tensor-core math allowed (set in bench())
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             logits = self.net(self.x)
         loss = F.cross_entropy(logits.float(), self.y)
         self.flat.zero_()
@@ -147,10 +149,13 @@ def bench(args, metric, ClockSampler, physical_gpu_index) -> dict:
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     torch.backends.cudnn.benchmark = True
+    if args.dtype == "fp32":                      # the same arithmetic our fp32 path uses
+        torch.backends.cuda.matmul.allow_tf32 = True
+        torch.backends.cudnn.allow_tf32 = True
     if n > 1:
         dist.init_process_group("nccl", device_id=dev)
     B, K, W = args.batch, args.steps, max(args.warmup, 3)
-    st = Step(args.model, B, args.rows, n, dev, args.optimizer, graph=not args.no_graph)
+    st = Step(args.model, B, args.rows, n, dev, args.optimizer, graph=not args.no_graph, dtype=args.dtype)
     st.warm(3)
     for _ in range(W):
         st.step()
@@ -196,7 +201,8 @@ def bench(args, metric, ClockSampler, physical_gpu_index) -> dict:
            "dtype": args.dtype, "data": "synthetic", "impl": "baseline",
            "config": {"model": f"mnist_cnn_{args.model}", "global_batch": n * B, "per_rank_batch": B, "seq_len": 784,
                       "parallelism": f"dp{n}", "optimizer": args.optimizer, "cuda_graph": not args.no_graph,
-                      "stack": "torch cuDNN/cuBLAS bf16 autocast + NCCL all_reduce + foreach optimizer",
+                      "stack": ("torch cuDNN/cuBLAS bf16 autocast" if args.dtype != "fp32" else "torch cuDNN/cuBLAS fp32 (TF32 allowed)")
+                               + " + NCCL all_reduce + foreach optimizer",
                       "loss_last": float(st.loss.item())},
            "clocks": sampler.summary(), "gpu_launches": 0}
     if e2e:

@@ -247,6 +247,9 @@ def run_ours(args) -> dict:
                    "parallelism": f"dp{n}", "optimizer": args.optimizer, "cuda_graph": cfg.cuda_graph,
                    "l2": "inputs larger than L2: 172 MB per-rank shard streamed sequentially, no flush",
                    "comm": "fused P2P allreduce+update kernel" if n > 1 else "fused update kernel",
+                   "math": ("fp32 storage and accumulation, TF32 tensor-core operands (kind::tf32), fp32 CUDA cores for "
+                            "conv1 and the loss head") if args.dtype == "fp32" else
+                           "bf16 tensor-core operands, fp32 accumulation, fp32 master weights and optimizer",
                    "loss_first": first, "loss_last": last},
         "clocks": sampler.summary(),
         "gpu_launches": int(launches),

@@ -115,6 +115,12 @@ __device__ inline uint4 dropout_words(uint32_t blk, uint64_t seed, uint64_t step
                      (uint32_t)(seed >> 32));
 }
 
+// element access for kernels instantiated for both activation types (bf16 and fp32)
+__device__ __forceinline__ float ldf(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ float ldf(const float* p) { return *p; }
+__device__ __forceinline__ void stf(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+__device__ __forceinline__ void stf(float* p, float v) { *p = v; }
+
 __device__ inline float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

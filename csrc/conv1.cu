@@ -23,10 +23,11 @@ __device__ __forceinline__ void load_padded_image(float* s_img, const float* __r
   }
 }
 
-// out [B,14,14,C1] bf16, idx [B,14,14,C1] u8 (2*dy+dx, first max wins), x [B,28,28] fp32
+// out [B,14,14,C1] bf16 or fp32, idx [B,14,14,C1] u8 (2*dy+dx, first max wins), x [B,28,28] fp32
+template <class T>
 __global__ void __launch_bounds__(256)
 conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25,C1]*/, const float* __restrict__ bias,
-                 __nv_bfloat16* __restrict__ out, uint8_t* __restrict__ idx, int B, int C1) {
+                 T* __restrict__ out, uint8_t* __restrict__ idx, int B, int C1) {
   __shared__ float s_img[PW * PW];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int groups = C1 / 32;
@@ -61,7 +62,7 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25,
         if (a10 > m) { m = a10; k = 2; }
         if (a11 > m) { m = a11; k = 3; }
         const size_t o = (((size_t)b * POOLED + pi) * POOLED + pj) * C1 + c;
-        out[o] = __float2bfloat16(m);
+        stf(out + o, m);
         idx[o] = (uint8_t)k;
       }
     }
@@ -69,10 +70,10 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25,
 }
 
 // dW[25,C1] += sum x[patch at argmax] * g,  db[C1] += sum g, with g = dP * [P > 0]
-// dP, P: [B,14,14,C1] bf16; idx u8.  Persistent blocks; one atomic per (tap, c) per block.
+// dP, P: [B,14,14,C1] bf16 or fp32; idx u8.  Persistent blocks; one atomic per (tap, c) per block.
+template <class T>
 __global__ void __launch_bounds__(256)
-conv1_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ dP,
-                   const __nv_bfloat16* __restrict__ P, const uint8_t* __restrict__ idx, float* __restrict__ dW,
+conv1_wgrad_kernel(const float* __restrict__ x, const T* __restrict__ dP, const T* __restrict__ P, const uint8_t* __restrict__ idx, float* __restrict__ dW,
                    float* __restrict__ db, int B, int C1) {
   __shared__ float s_img[PW * PW];
   __shared__ float s_red[8][26][33];
@@ -91,8 +92,8 @@ conv1_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict_
       for (int item = warp; item < POOLED * POOLED; item += nwarps) {
         const int pi = item / POOLED, pj = item % POOLED;
         const size_t o = (((size_t)b * POOLED + pi) * POOLED + pj) * C1 + c;
-        float gv = __bfloat162float(dP[o]);
-        if (!(__bfloat162float(P[o]) > 0.f)) gv = 0.f;
+        float gv = ldf(dP + o);
+        if (!(ldf(P + o) > 0.f)) gv = 0.f;
         const int k = idx[o];
         accb += gv;
         const float* p = s_img + (2 * pi) * PW + 2 * pj;
@@ -138,6 +139,15 @@ int mtb_conv1_fwd(const float* x, const float* w, const float* bias, void* out_b
   return 0;
 }
 
+int mtb_conv1_fwd_f32(const float* x, const float* w, const float* bias, float* out, uint8_t* idx, int B, int C1,
+                      cudaStream_t stream) {
+  MTB_REQUIRE(C1 % 32 == 0 && B > 0, "conv1_fwd: C1 must be a multiple of 32");
+  int grid = B < 148 * 4 ? B : 148 * 4;
+  conv1_fwd_kernel<<<grid, 256, 0, stream>>>(x, w, bias, out, idx, B, C1);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
 // dW and db are ACCUMULATED into (caller zeroes them once per step).
 int mtb_conv1_wgrad(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
                     int B, int C1, cudaStream_t stream) {
@@ -145,6 +155,15 @@ int mtb_conv1_wgrad(const float* x, const void* dP_bf16, const void* P_bf16, con
   int grid = B < 148 * 2 ? B : 148 * 2;
   conv1_wgrad_kernel<<<grid, 256, 0, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(dP_bf16),
                                                reinterpret_cast<const __nv_bfloat16*>(P_bf16), idx, dW, db, B, C1);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_conv1_wgrad_f32(const float* x, const float* dP, const float* P, const uint8_t* idx, float* dW, float* db,
+                        int B, int C1, cudaStream_t stream) {
+  MTB_REQUIRE(C1 % 32 == 0 && B > 0, "conv1_wgrad: C1 must be a multiple of 32");
+  int grid = B < 148 * 2 ? B : 148 * 2;
+  conv1_wgrad_kernel<<<grid, 256, 0, stream>>>(x, dP, P, idx, dW, db, B, C1);
   MTB_LAUNCH_CHECK();
   return 0;
 }

@@ -108,13 +108,20 @@ __device__ __forceinline__ void epilogue_store(const GemmParams& p, const float 
 // loads 1/CN of the A tile, multicast to all of them; the CM CTAs of a cluster column share the
 // B tile the same way.  L2 -> SM traffic per CTA drops from A+B to A/CN + B/CM, which is what
 // bounds these GEMMs (tiles are small because the batch is).
-template <int BN, bool A_MN, bool B_MN, int CM, int CN>
+// TF32 = true: fp32 operands in shared memory, kind::tf32 MMAs (K = 8 per instruction).  A 128-byte swizzle row
+// then holds 32 elements instead of 64, so a stage covers 32 K and an MN-major atom is 32 elements wide; the
+// byte geometry (16 KB of A per stage, 32 bytes of K per MMA in K-major form) is the same as for bf16.
+template <int BN, bool A_MN, bool B_MN, int CM, int CN, bool TF32 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const GemmParams p) {
   using C = Cfg<BN>;
   constexpr int S = C::kStages;
   constexpr bool kCluster = CM * CN > 1;
+  static_assert(!(TF32 && kCluster), "the multicast variants are bf16 only");
+  constexpr int kBKe = TF32 ? 32 : 64;             // K elements per stage (one 128-byte row)
+  constexpr int kBlkE = TF32 ? 32 : 64;            // MN elements per MN-major atom column
+  constexpr int kBlkBytes = kBKe * 128;            // one MN-major block: kBKe K-rows of 128 bytes
   const int cx = CM > 1 ? (int)(blockIdx.x % CM) : 0, cy = CN > 1 ? (int)(blockIdx.y % CN) : 0;
   uint16_t row_mask = 0, col_mask = 0;            // cluster ranks (x + y*CM) that share my A / my B
 #pragma unroll
@@ -158,15 +165,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         const int s = i % S, ph = (i / S) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         mbar_arrive_expect_tx(&full_bar[s], C::kABytes + C::kBBytes);
-        const int kc = (kb0 + i) * BK;
+        const int kc = (kb0 + i) * kBKe;
         uint8_t* a = sA + s * C::kABytes;
         uint8_t* b = sB + s * C::kBBytes;
         if (CN == 1) {
           if (!A_MN) {
             tma_load_2d(a, &tma_a, &full_bar[s], kc, tile_m * BM);
           } else {
-            tma_load_2d(a, &tma_a, &full_bar[s], tile_m * BM, kc);
-            tma_load_2d(a + 8192, &tma_a, &full_bar[s], tile_m * BM + 64, kc);
+#pragma unroll
+            for (int h = 0; h < BM / kBlkE; ++h)
+              tma_load_2d(a + h * kBlkBytes, &tma_a, &full_bar[s], tile_m * BM + h * kBlkE, kc);
           }
         } else if (!A_MN) {                        // my BM/CN rows of the K-major tile, to the whole cluster row
           constexpr int R = BM / CN;
@@ -182,7 +190,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             tma_load_2d(b, &tma_b, &full_bar[s], kc, tile_n * BN);
           } else {
 #pragma unroll
-            for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tma_b, &full_bar[s], tile_n * BN + h * 64, kc);
+            for (int h = 0; h < BN / kBlkE; ++h)
+              tma_load_2d(b + h * kBlkBytes, &tma_b, &full_bar[s], tile_n * BN + h * kBlkE, kc);
           }
         } else if (!B_MN) {
           constexpr int R = BN / CM;
@@ -198,23 +207,35 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     __syncwarp();
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc(kFmtBF16, BM, BN, A_MN, B_MN);
-      // one descriptor per operand; stages and K steps only move the 14-bit start-address field
-      const uint64_t da0 = A_MN ? make_smem_desc(smem_u32(sA), 8192, 1024, kSwizzle128B)
+      constexpr uint32_t idesc = make_idesc(TF32 ? kFmtTF32 : kFmtBF16, BM, BN, A_MN, B_MN);
+      // one descriptor per operand; stages and K steps only move the 14-bit start-address field.
+      // MN-major: LBO = stride between atom columns, SBO = stride between 8-row K groups; one MMA covers
+      // 16 (bf16) or 8 (tf32) K rows = two or one such group.
+      // tf32 MN-major operands only exist in the 32-byte-chunk flavour of the 128-byte swizzle (atoms of 4 K rows,
+      // SBO = 512): TMA writes it with SWIZZLE_128B_ATOM_32B.
+      constexpr uint32_t kMnSwz = TF32 ? kSwizzle128B_Base32B : kSwizzle128B;
+      constexpr uint32_t kMnSbo = TF32 ? 512 : 1024;
+      const uint64_t da0 = A_MN ? make_smem_desc(smem_u32(sA), kBlkBytes, kMnSbo, kMnSwz)
                                 : make_smem_desc(smem_u32(sA), 16, 1024, kSwizzle128B);
-      const uint64_t db0 = B_MN ? make_smem_desc(smem_u32(sB), 8192, 1024, kSwizzle128B)
+      const uint64_t db0 = B_MN ? make_smem_desc(smem_u32(sB), kBlkBytes, kMnSbo, kMnSwz)
                                 : make_smem_desc(smem_u32(sB), 16, 1024, kSwizzle128B);
-      constexpr uint32_t a_kstep = (A_MN ? 2048 : 32) >> 4, b_kstep = (B_MN ? 2048 : 32) >> 4;
+      constexpr uint32_t kMnStep = TF32 ? 1024 : 2048;
+      constexpr uint32_t a_kstep = (A_MN ? kMnStep : 32) >> 4, b_kstep = (B_MN ? kMnStep : 32) >> 4;
       int s = 0, ph = 0;
       for (int i = 0; i < nkb; ++i) {
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         const uint64_t da = da0 + (uint64_t)((uint32_t)(s * C::kABytes) >> 4);
         const uint64_t db = db0 + (uint64_t)((uint32_t)(s * C::kBBytes) >> 4);
-        if (i == 0) mma_f16_first(tmem_base, da, db, idesc);
-        else mma_f16_acc(tmem_base, da, db, idesc);
+        if (TF32) {
 #pragma unroll
-        for (int k = 1; k < BK / 16; ++k) mma_f16_acc(tmem_base, da + k * a_kstep, db + k * b_kstep, idesc);
+          for (int k = 0; k < 4; ++k) mma_tf32(tmem_base, da + k * a_kstep, db + k * b_kstep, idesc, i > 0 || k > 0);
+        } else {
+          if (i == 0) mma_f16_first(tmem_base, da, db, idesc);
+          else mma_f16_acc(tmem_base, da, db, idesc);
+#pragma unroll
+          for (int k = 1; k < BK / 16; ++k) mma_f16_acc(tmem_base, da + k * a_kstep, db + k * b_kstep, idesc);
+        }
         // smem slot reusable once these MMAs retire: tell every CTA that multicasts into it
         if (kCluster) mma_commit_mc(&empty_bar[s], row_mask | col_mask);
         else mma_commit(&empty_bar[s]);
@@ -297,33 +318,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 
 // ---- tensor-map cache ------------------------------------------------------------------------
 struct MapKey {
-  const void* base; uint64_t rows, cols, pitch; uint32_t box_rows, box_cols;
+  const void* base; uint64_t rows, cols, pitch; uint32_t box_rows, box_cols; int elem_bytes; bool atom32;
   bool operator<(const MapKey& o) const {
-    return std::tie(base, rows, cols, pitch, box_rows, box_cols) <
-           std::tie(o.base, o.rows, o.cols, o.pitch, o.box_rows, o.box_cols);
+    return std::tie(base, rows, cols, pitch, box_rows, box_cols, elem_bytes, atom32) <
+           std::tie(o.base, o.rows, o.cols, o.pitch, o.box_rows, o.box_cols, o.elem_bytes, o.atom32);
   }
 };
 std::map<MapKey, CUtensorMap> g_maps;
 std::mutex g_maps_mu;
 
 bool get_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
-             uint32_t box_rows, uint32_t box_cols) {
+             uint32_t box_rows, uint32_t box_cols, int elem_bytes = 2, bool atom32 = false) {
   std::lock_guard<std::mutex> lk(g_maps_mu);
-  MapKey k{base, rows, cols, pitch_bytes, box_rows, box_cols};
+  MapKey k{base, rows, cols, pitch_bytes, box_rows, box_cols, elem_bytes, atom32};
   auto it = g_maps.find(k);
   if (it != g_maps.end()) { *out = it->second; return true; }
   CUtensorMap m;
-  if (!tma::make_2d_sw128(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, rows, cols, pitch_bytes, box_rows, box_cols))
-    return false;
+  const CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const CUtensorMapSwizzle swz = atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  if (!tma::make_2d_sw128(&m, dt, elem_bytes, base, rows, cols, pitch_bytes, box_rows, box_cols, swz)) return false;
   if (g_maps.size() > 4096) g_maps.clear();
   g_maps[k] = m;
   *out = m;
   return true;
 }
 
-template <int BN, bool A_MN, bool B_MN, int CM = 1, int CN = 1>
+template <int BN, bool A_MN, bool B_MN, int CM = 1, int CN = 1, bool TF32 = false>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CM, CN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CM, CN, TF32>;
   static bool attr_set = false;
   if (!attr_set) {
     MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
@@ -412,6 +434,51 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   MTB_GEMM_CASE(256, true, true)
 #undef MTB_GEMM_CASE
   return mtb_set_error_msg(MTB_E_ARG, "gemm: no kernel variant", __FILE__, __LINE__);
+}
+
+// fp32 operands, TF32 tensor-core math, fp32 accumulation and output (the "fp32" configs of BASELINE.json; the
+// reference's own matmuls are fp32 cuBLAS sgemm, mpipy.py:165,167).  Same operand-major options, split-K and
+// epilogue as mtb_gemm_bf16; lda/ldb/ldc in elements.
+int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int K, int a_mn_major, int b_mn_major,
+                  long long lda, long long ldb, long long ldc, const float* bias, int relu, float keep_prob,
+                  unsigned long long seed, const long long* step_ptr, int bn, int splits, void* workspace,
+                  void* counters, cudaStream_t stream) {
+  MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm_tf32: null pointer or empty shape");
+  MTB_REQUIRE((lda * 4) % 16 == 0 && (ldb * 4) % 16 == 0, "gemm_tf32: operand row pitch must be a multiple of 16 bytes");
+  MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_tf32: operands must be 16-byte aligned");
+  if (bn != 64 && bn != 128 && bn != 256) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
+  if (splits < 1) splits = 1;
+  constexpr int kBKe = 32;
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_total = (int)mtb::ceil_div(K, kBKe);
+  if (splits > p.kb_total) splits = p.kb_total;
+  p.kb_per_split = (int)mtb::ceil_div(p.kb_total, splits);
+  splits = (int)mtb::ceil_div(p.kb_total, p.kb_per_split);
+  p.splits = splits;
+  MTB_REQUIRE(splits == 1 || (workspace && counters), "gemm_tf32: split-K needs workspace and counters");
+  p.out = out; p.ldc = ldc; p.out_bf16 = 0; p.bias = bias; p.relu = relu;
+  p.keep_prob = keep_prob; p.seed = seed; p.step_ptr = step_ptr;
+  p.workspace = reinterpret_cast<float*>(workspace);
+  p.counters = reinterpret_cast<unsigned int*>(counters);
+  CUtensorMap ma, mb;
+  bool ok;
+  ok = a_mn_major ? get_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 4, kBKe, 32, 4, true)
+                  : get_map(&ma, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 4, BM, 32, 4);
+  MTB_REQUIRE(ok, "gemm_tf32: cuTensorMapEncodeTiled failed for A");
+  ok = b_mn_major ? get_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 4, kBKe, 32, 4, true)
+                  : get_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 4, (uint32_t)bn, 32, 4);
+  MTB_REQUIRE(ok, "gemm_tf32: cuTensorMapEncodeTiled failed for B");
+#define MTB_GEMM_CASE(BN_, AM_, BM_)                                            \
+  if (bn == BN_ && (a_mn_major != 0) == AM_ && (b_mn_major != 0) == BM_)        \
+    return launch<BN_, AM_, BM_, 1, 1, true>(ma, mb, p, stream);
+  MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)
+  MTB_GEMM_CASE(128, true, true) MTB_GEMM_CASE(64, false, false) MTB_GEMM_CASE(64, false, true)
+  MTB_GEMM_CASE(64, true, false) MTB_GEMM_CASE(64, true, true)
+  MTB_GEMM_CASE(256, false, false) MTB_GEMM_CASE(256, false, true) MTB_GEMM_CASE(256, true, false)
+  MTB_GEMM_CASE(256, true, true)
+#undef MTB_GEMM_CASE
+  return mtb_set_error_msg(MTB_E_ARG, "gemm_tf32: no kernel variant", __FILE__, __LINE__);
 }
 
 }  // extern "C"

@@ -18,9 +18,10 @@ __device__ long long g_trace2[64];
 #define TRACE2(i) do { } while (0)
 #endif
 
-// one warp per row
+// one warp per row; T = activation type (bf16 or fp32)
+template <class T>
 __global__ void __launch_bounds__(256)
-fc2_softmax_ce_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
+fc2_softmax_ce_kernel(const T* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
                       const float* __restrict__ bias, const int* __restrict__ labels, float* __restrict__ logits,
                       float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ loss_accum,
                       int* __restrict__ err_accum, int B, int F, int NC) {
@@ -29,9 +30,9 @@ fc2_softmax_ce_kernel(const __nv_bfloat16* __restrict__ h, const float* __restri
   float acc[kMaxClasses];
 #pragma unroll
   for (int c = 0; c < kMaxClasses; ++c) acc[c] = 0.f;
-  const __nv_bfloat16* hr = h + (size_t)warp * F;
+  const T* hr = h + (size_t)warp * F;
   for (int f = lane; f < F; f += 32) {
-    const float hv = __bfloat162float(hr[f]);
+    const float hv = ldf(hr + f);
     const float* wr = W + (size_t)f * NC;
 #pragma unroll
     for (int c = 0; c < kMaxClasses; ++c)
@@ -82,9 +83,10 @@ fc2_softmax_ce_kernel(const __nv_bfloat16* __restrict__ h, const float* __restri
 }
 
 // dh[b,f] = (sum_c dlogits[b,c] * W[f,c]) * (h[b,f] > 0 ? scale : 0)   -> bf16
+template <class T>
 __global__ void __launch_bounds__(256)
-fc2_dgrad_kernel(const float* __restrict__ dlogits, const float* __restrict__ W, const __nv_bfloat16* __restrict__ h,
-                 __nv_bfloat16* __restrict__ dh, int B, int F, int NC, float scale) {
+fc2_dgrad_kernel(const float* __restrict__ dlogits, const float* __restrict__ W, const T* __restrict__ h,
+                 T* __restrict__ dh, int B, int F, int NC, float scale) {
   const int b = blockIdx.y;
   __shared__ float dl[kMaxClasses];
   if (threadIdx.x < NC) dl[threadIdx.x] = dlogits[(size_t)b * NC + threadIdx.x];
@@ -93,14 +95,15 @@ fc2_dgrad_kernel(const float* __restrict__ dlogits, const float* __restrict__ W,
     float acc = 0.f;
     const float* wr = W + (size_t)f * NC;
     for (int c = 0; c < NC; ++c) acc = fmaf(dl[c], __ldg(wr + c), acc);
-    const float hv = __bfloat162float(h[(size_t)b * F + f]);
-    dh[(size_t)b * F + f] = __float2bfloat16(hv > 0.f ? acc * scale : 0.f);
+    const float hv = ldf(h + (size_t)b * F + f);
+    stf(dh + (size_t)b * F + f, hv > 0.f ? acc * scale : 0.f);
   }
 }
 
 // dW[f,c] += sum_b h[b,f]*dlogits[b,c];  db[c] += sum_b dlogits[b,c].  lanes <-> f.
+template <class T>
 __global__ void __launch_bounds__(128)
-fc2_wgrad_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ dlogits, float* __restrict__ dW,
+fc2_wgrad_kernel(const T* __restrict__ h, const float* __restrict__ dlogits, float* __restrict__ dW,
                  float* __restrict__ db, int B, int F, int NC, int rows_per_block) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   const int b0 = blockIdx.y * rows_per_block, b1 = min(B, b0 + rows_per_block);
@@ -112,7 +115,7 @@ fc2_wgrad_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ 
   for (int b = b0; b < b1; ++b) {
     const float* dl = dlogits + (size_t)b * NC;
     if (f < F) {
-      const float hv = __bfloat162float(h[(size_t)b * F + f]);
+      const float hv = ldf(h + (size_t)b * F + f);
 #pragma unroll
       for (int c = 0; c < kMaxClasses; ++c)
         if (c < NC) acc[c] = fmaf(hv, __ldg(dl + c), acc[c]);
@@ -128,15 +131,16 @@ fc2_wgrad_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ 
 }
 
 // out[c] += sum_r x[r,c]   (bias gradients, SURVEY O18/O20 "BiasAddGrad")
+template <class T>
 __global__ void __launch_bounds__(256)
-colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, long long R, int C,
+colsum_bf16_kernel(const T* __restrict__ x, float* __restrict__ out, long long R, int C,
                    int rows_per_block) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const long long r0 = (long long)blockIdx.y * rows_per_block;
   const long long r1 = r0 + rows_per_block < R ? r0 + rows_per_block : R;
   float acc = 0.f;
-  for (long long r = r0; r < r1; ++r) acc += __bfloat162float(x[r * C + c]);
+  for (long long r = r0; r < r1; ++r) acc += ldf(x + r * C + c);
   atomicAdd(out + c, acc);
 }
 
@@ -413,6 +417,45 @@ int mtb_fc2_wgrad(const void* h_bf16, const float* dlogits, float* dW, float* db
   dim3 grid((F + 127) / 128, (B + rows_per_block - 1) / rows_per_block);
   fc2_wgrad_kernel<<<grid, 128, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(h_bf16), dlogits, dW, db, B, F,
                                              NC, rows_per_block);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---- fp32-activation twins of the four generic kernels (TF32 / fp32 training path) ----
+int mtb_fc2_softmax_ce_f32(const float* h, const float* W, const float* bias, const int* labels, float* logits,
+                           float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
+                           cudaStream_t stream) {
+  MTB_REQUIRE(NC > 0 && NC <= kMaxClasses, "fc2_softmax_ce: at most 16 classes");
+  const int warps_per_block = 8;
+  fc2_softmax_ce_kernel<<<(B + warps_per_block - 1) / warps_per_block, 256, 0, stream>>>(
+      h, W, bias, labels, logits, probs, dlogits, loss_accum, err_accum, B, F, NC);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_fc2_dgrad_f32(const float* dlogits, const float* W, const float* h, float* dh, int B, int F, int NC,
+                      float scale, cudaStream_t stream) {
+  MTB_REQUIRE(NC > 0 && NC <= kMaxClasses, "fc2_dgrad: at most 16 classes");
+  dim3 grid((F + 255) / 256, B);
+  fc2_dgrad_kernel<<<grid, 256, 0, stream>>>(dlogits, W, h, dh, B, F, NC, scale);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_fc2_wgrad_f32(const float* h, const float* dlogits, float* dW, float* db, int B, int F, int NC,
+                      cudaStream_t stream) {
+  MTB_REQUIRE(NC > 0 && NC <= kMaxClasses, "fc2_wgrad: at most 16 classes");
+  int rows_per_block = 32;
+  dim3 grid((F + 127) / 128, (B + rows_per_block - 1) / rows_per_block);
+  fc2_wgrad_kernel<<<grid, 128, 0, stream>>>(h, dlogits, dW, db, B, F, NC, rows_per_block);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
+
+int mtb_colsum_f32(const float* x, float* out, long long R, int C, cudaStream_t stream) {
+  int rows_per_block = 64;
+  dim3 grid((C + 255) / 256, (unsigned)((R + rows_per_block - 1) / rows_per_block));
+  colsum_bf16_kernel<<<grid, 256, 0, stream>>>(x, out, R, C, rows_per_block);
   MTB_LAUNCH_CHECK();
   return 0;
 }

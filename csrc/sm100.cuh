@@ -202,7 +202,8 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16])
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------- descriptors
-enum : uint32_t { kSwizzleNone = 0, kSwizzle128B = 2, kSwizzle64B = 4, kSwizzle32B = 6 };
+// kSwizzle128B_Base32B: 32-byte chunks swizzled over 4-row (512 B) atoms, the only layout MN-major tf32 operands accept
+enum : uint32_t { kSwizzleNone = 0, kSwizzle128B_Base32B = 1, kSwizzle128B = 2, kSwizzle64B = 4, kSwizzle32B = 6 };
 
 // Shared-memory matrix descriptor (64 bit).  Offsets are in bytes, multiples of 16.
 //   K-major  : LBO = stride between the two 16-byte K chunks (no-swizzle only), SBO = stride between 8-row groups

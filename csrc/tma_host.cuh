@@ -42,12 +42,13 @@ inline bool make(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void*
 // Row-major matrix [rows, cols] (cols contiguous), box = [box_rows, box_cols], 128B swizzle:
 // box_cols * elem_size must be exactly 128 bytes.
 inline bool make_2d_sw128(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, const void* base, uint64_t rows,
-                          uint64_t cols, uint64_t row_pitch_bytes, uint32_t box_rows, uint32_t box_cols) {
+                          uint64_t cols, uint64_t row_pitch_bytes, uint32_t box_rows, uint32_t box_cols,
+                          CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   uint64_t dims[2] = {cols, rows};
   uint64_t strides[1] = {row_pitch_bytes};
   uint32_t box[2] = {box_cols, box_rows};
   (void)elem_bytes;
-  return make(out, dt, 2, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+  return make(out, dt, 2, base, dims, strides, box, swz);
 }
 
 }  // namespace tma

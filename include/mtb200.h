@@ -47,6 +47,11 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
                   long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
                   float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
                   void* workspace, void* counters, cudaStream_t stream);
+/* fp32 operands and output, TF32 tensor-core math (kind::tf32), fp32 accumulation: the fp32 training path. */
+int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int K, int a_mn_major, int b_mn_major,
+                  long long lda, long long ldb, long long ldc, const float* bias, int relu, float keep_prob,
+                  unsigned long long seed, const long long* step_ptr, int bn, int splits, void* workspace,
+                  void* counters, cudaStream_t stream);
 
 /* Split-K GEMM with built-in scratch, for callers that cannot allocate or pass device scratch (a plug-in inside a
  * process whose allocator owns the whole GPU, an allocation-free control loop, a bare C caller without a tensor
@@ -141,6 +146,26 @@ int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bia
 int mtb_fc2_bwd_fused(const void* h_bf16, const float* dlogits, const float* W, void* dh_bf16, float* dW, float* db2,
                       float* db1, int B, int F, int NC, float scale, cudaStream_t stream);
 int mtb_colsum_bf16(const void* x_bf16, float* out, long long R, int C, cudaStream_t stream);
+
+/* ---- fp32-activation twins of the generic layer kernels (the fp32 / TF32 training path: dtype="fp32").
+ * Same semantics and layouts as the functions of the same name without the suffix; every tensor is fp32. */
+int mtb_conv1_fwd_f32(const float* x, const float* w, const float* bias, float* out, uint8_t* idx, int B, int C1,
+                      cudaStream_t stream);
+int mtb_conv1_wgrad_f32(const float* x, const float* dP, const float* P, const uint8_t* idx, float* dW, float* db,
+                        int B, int C1, cudaStream_t stream);
+int mtb_maxpool2x2_fwd_f32(const float* in, float* out, uint8_t* idx, int B, int H, int W, int C, cudaStream_t stream);
+int mtb_unpool_relu_bwd_f32(const float* dP, const float* P, const uint8_t* idx, float* dA, int B, int H, int W, int C,
+                            cudaStream_t stream);
+int mtb_im2col_5x5_f32(const float* x, float* col, int B, int H, int W, int C, cudaStream_t stream);
+int mtb_col2im_5x5_f32(const float* dcol, float* dx, int B, int H, int W, int C, cudaStream_t stream);
+int mtb_fc2_softmax_ce_f32(const float* h, const float* W, const float* bias, const int* labels, float* logits,
+                           float* probs, float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC,
+                           cudaStream_t stream);
+int mtb_fc2_dgrad_f32(const float* dlogits, const float* W, const float* h, float* dh, int B, int F, int NC,
+                      float scale, cudaStream_t stream);
+int mtb_fc2_wgrad_f32(const float* h, const float* dlogits, float* dW, float* db, int B, int F, int NC,
+                      cudaStream_t stream);
+int mtb_colsum_f32(const float* x, float* out, long long R, int C, cudaStream_t stream);
 
 /* ---- K1: fused cross-GPU allreduce + average + L2 + optimizer + LR schedule + bf16 cast
  *      (Gather/mean/assign mpipy.py:121-152; l2 mpipy.py:57-58; lr mpipy.py:60-64; momentum mpipy.py:65) */

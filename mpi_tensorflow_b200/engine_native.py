@@ -42,10 +42,11 @@ class NativeEngine:
         N.lib()                                   # fail loudly if the extension is missing
         if cfg.comm_dtype != "fp32":
             raise NotImplementedError("comm_dtype='bf16' is not implemented: gradients cross NVLink in fp32")
-        if cfg.dtype == "fp32":
-            import warnings
-            warnings.warn("the GPU engine has no fp32/TF32 compute path: running bf16 tensor-core operands with fp32 "
-                          "accumulation, fp32 master weights and fp32 optimizer state", stacklevel=2)
+        if cfg.dtype not in ("bf16", "fp32"):
+            raise ValueError(f"dtype must be 'bf16' or 'fp32', got {cfg.dtype!r}")
+        # fp32: every activation, weight operand and gradient is fp32; the GEMM-shaped products run as TF32
+        # tensor-core MMAs with fp32 accumulation, conv1 (K = 25) and the loss head on fp32 CUDA cores.
+        self.fp32 = cfg.dtype == "fp32"
         self.spec, self.cfg, self.comm, self.device = spec, cfg, comm, device
         torch.cuda.set_device(device)
         self.B = cfg.batch
@@ -104,7 +105,9 @@ class NativeEngine:
         self._zero_args = None
         self._scratch = {}
         self._masters_dirty = self._slots_dirty = False
-        self._shard_master = bool(self.cfg.shard_master) and self.p2p is not None and self.world > 1
+        # fp32 path: consumers read the fp32 master itself, so every rank needs all of it
+        self._shard_master = (bool(self.cfg.shard_master) and self.p2p is not None and self.world > 1
+                              and not self.fp32)
         self._done = torch.zeros(1, dtype=torch.int32, device=dev)
         # loss mailbox: K1's last block stores {step, loss} words straight into this pinned host ring
         self._mail = torch.zeros(self._MAIL_RING, dtype=torch.int64).pin_memory()
@@ -122,7 +125,8 @@ class NativeEngine:
 
     def _alloc_activations(self, Bmax: int):
         s, dev = self.spec, self.device
-        bf, f32 = torch.bfloat16, torch.float32
+        f32 = torch.float32
+        bf = f32 if self.fp32 else torch.bfloat16                       # activation dtype
         z = lambda *shape, dtype=bf: torch.zeros(*shape, dtype=dtype, device=dev)  # noqa: E731
         self.Bmax = Bmax
         self.x_in = z(Bmax, 784, dtype=f32)
@@ -136,15 +140,18 @@ class NativeEngine:
         self.da2 = z(Bmax, 14, 14, s.c2)
         self.dp1 = z(Bmax, 14, 14, s.c1)
         # conv1 on tensor cores when it has 32 output channels, else the CUDA-core kernel
-        self.conv1_tc = s.c1 == 32 and self.conv_impl != "im2col"
-        self._fast_head = s.num_classes == 10 and s.fc % 128 == 0 and s.fc * 40 <= 170 * 1024
+        self.conv1_tc = s.c1 == 32 and self.conv_impl != "im2col" and not self.fp32
+        self._fast_head = s.num_classes == 10 and s.fc % 128 == 0 and s.fc * 40 <= 170 * 1024 and not self.fp32
+        # the generic layer kernels exist for both activation types; GEMMs are bf16 or TF32
+        self._sfx = "_f32" if self.fp32 else ""
+        self._gemm = N.gemm_tf32 if self.fp32 else N.gemm_bf16
         # batch window fused into the kernels that read the batch (needs both fast paths)
         self._can_window = self.conv1_tc and self._fast_head
         self._windowed = False
         self._stream_buf = None
         # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
         want = self.conv_impl
-        have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2))
+        have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2)) and not self.fp32
         if want == "implicit" and not have:
             raise ValueError(f"no implicit-GEMM conv2 kernel for {s.c1}->{s.c2} channels")
         self.conv2_implicit = have and want != "im2col"
@@ -173,6 +180,8 @@ class NativeEngine:
 
     def params_changed(self):
         """Refresh the bf16 shadow after the fp32 master was written from outside K1."""
+        if self.fp32:
+            return                                # no shadow: the kernels read the master
         N.call("mtb_cast_f32_to_bf16", self.flat_params.data_ptr(), self.shadow.data_ptr(), self.n)
 
     def synchronize(self):
@@ -283,7 +292,9 @@ class NativeEngine:
 
     def _forward(self, B: int, train: bool, with_loss: bool, zero: bool = False):
         s, c = self.spec, self.cfg
-        P, S = self.P, self.S
+        P = self.P
+        S = self.P if self.fp32 else self.S       # weight operands of the GEMM-shaped products
+        sfx, gemm = self._sfx, self._gemm
         keep = s.keep_prob if (train and c.dropout) else 1.0
         wx, wy, wstep, wrows = self._win()
         # conv1 + bias + ReLU + pool (mpipy.py:156-158)
@@ -296,7 +307,7 @@ class NativeEngine:
             N.call("mtb_conv1_fwd_tc_win", wx, P["conv1_weight"].data_ptr(),
                    P["conv1_bias"].data_ptr(), self.a1p.data_ptr(), self.idx1.data_ptr(), B, wstep, wrows)
         else:
-            N.call("mtb_conv1_fwd", self.x_in.data_ptr(), P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
+            N.call("mtb_conv1_fwd" + sfx, wx, P["conv1_weight"].data_ptr(), P["conv1_bias"].data_ptr(),
                    self.a1p.data_ptr(), self.idx1.data_ptr(), B, s.c1)
         # conv2 + bias + ReLU + pool (mpipy.py:159-161)
         M2, K2 = B * 196, 25 * s.c1
@@ -304,10 +315,10 @@ class NativeEngine:
             N.call("mtb_conv2_fprop_pool", self.a1p.data_ptr(), S["conv2_weight"].data_ptr(),
                    P["conv2_bias"].data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B)
         else:
-            N.call("mtb_im2col_5x5", self.a1p.data_ptr(), self.col.data_ptr(), B, 14, 14, s.c1)
-            N.gemm_bf16(self.col, S["conv2_weight"].view(K2, s.c2), self.a2, M2, s.c2, K2, False, True,
-                        bias=P["conv2_bias"], relu=True)
-            N.call("mtb_maxpool2x2_fwd", self.a2.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B, 14, 14,
+            N.call("mtb_im2col_5x5" + sfx, self.a1p.data_ptr(), self.col.data_ptr(), B, 14, 14, s.c1)
+            gemm(self.col, S["conv2_weight"].view(K2, s.c2), self.a2, M2, s.c2, K2, False, True,
+                 bias=P["conv2_bias"], relu=True)
+            N.call("mtb_maxpool2x2_fwd" + sfx, self.a2.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B, 14, 14,
                    s.c2)
         # FC1 + bias + ReLU + dropout in the GEMM epilogue (mpipy.py:165-166)
         flat = self.a2p.view(self.Bmax, s.flat_dim)
@@ -318,9 +329,8 @@ class NativeEngine:
             # last-arriver reduction costs more than the idle SMs), so opt-in only.
             splits = max(1, min(8, 128 // tiles))
         ws, cnt = self._splitk_scratch("fc1_fprop", B, s.fc, bn, splits)
-        N.gemm_bf16(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
-                    keep_prob=keep, seed=c.seed, step_ptr=self.dev_step, bn=bn, splits=splits, workspace=ws,
-                    counters=cnt)
+        gemm(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
+             keep_prob=keep, seed=c.seed, step_ptr=self.dev_step, bn=bn, splits=splits, workspace=ws, counters=cnt)
         # FC2 + softmax + CE + dlogits (mpipy.py:167, :55-56, :67)
         head = (self.h.data_ptr(), P["fc2_weight"].data_ptr(), P["fc2_bias"].data_ptr(),
                 wy if with_loss else None, self.logits.data_ptr(), self.probs.data_ptr(),
@@ -329,7 +339,7 @@ class NativeEngine:
         if self._fast_head:
             N.call("mtb_fc2_softmax_ce_fast_win", *head, wstep, wrows)
         else:
-            N.call("mtb_fc2_softmax_ce", *head)
+            N.call("mtb_fc2_softmax_ce" + sfx, *head)
 
     # ------------------------------------------------------------------ backward
     def _backward(self, B: int):
@@ -340,37 +350,41 @@ class NativeEngine:
         """FC2 and FC1 backward.  When it returns, every gradient of the fc bucket is final and no
         later kernel of the step reads an FC weight, so the bucket's fused update may start."""
         s, c = self.spec, self.cfg
-        P, S, G = self.P, self.S, self.G
+        P, G = self.P, self.G
+        S = self.P if self.fp32 else self.S
+        sfx, gemm = self._sfx, self._gemm
         scale = 1.0 / s.keep_prob if c.dropout else 1.0
         M2, K2 = B * 196, 25 * s.c1
         flat = self.a2p.view(self.Bmax, s.flat_dim)
-        if s.num_classes == 10:
+        if s.num_classes == 10 and not self.fp32:
             # dW2, db2, dh (with the dropout / ReLU mask) and db of FC1 in one pass over h
             N.call("mtb_fc2_bwd_fused", self.h.data_ptr(), self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(),
                    self.dh.data_ptr(), G["fc2_weight"].data_ptr(), G["fc2_bias"].data_ptr(),
                    G["fc1_bias"].data_ptr(), B, s.fc, s.num_classes, scale)
         else:
-            N.call("mtb_fc2_wgrad", self.h.data_ptr(), self.dlogits.data_ptr(), G["fc2_weight"].data_ptr(),
+            N.call("mtb_fc2_wgrad" + sfx, self.h.data_ptr(), self.dlogits.data_ptr(), G["fc2_weight"].data_ptr(),
                    G["fc2_bias"].data_ptr(), B, s.fc, s.num_classes)
-            N.call("mtb_fc2_dgrad", self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(), self.h.data_ptr(),
+            N.call("mtb_fc2_dgrad" + sfx, self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(), self.h.data_ptr(),
                    self.dh.data_ptr(), B, s.fc, s.num_classes, scale)
-            N.call("mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
+            N.call("mtb_colsum_f32" if self.fp32 else "mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
         # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand.  Runs BEFORE the
         # weight gradient so that the last reader of the FC1 weights is done when the bucket closes.
         bn = 256 if B >= 512 else 128
         tiles = -(-B // 128) * -(-s.flat_dim // bn)
         splits = max(1, min(4, 128 // tiles)) if (tiles < 64 and os.environ.get("MTB_FC_SPLITK") == "1") else 1
         ws, cnt = self._splitk_scratch("fc1_dgrad", B, s.flat_dim, bn, splits)
-        N.gemm_bf16(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=bn, splits=splits,
-                    workspace=ws, counters=cnt)
+        gemm(self.dh, S["fc1_weight"], self.dflat, B, s.flat_dim, s.fc, False, False, bn=bn, splits=splits,
+             workspace=ws, counters=cnt)
         # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket (K = batch: wide tiles
         # only pay off when K is long enough to amortise their epilogue)
-        N.gemm_bf16(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True,
-                    bn=256 if (s.fc % 256 == 0 and B >= 512) else 128)
+        gemm(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True,
+             bn=256 if (s.fc % 256 == 0 and B >= 512) else 128)
 
     def _backward_conv(self, B: int):
         s = self.spec
-        P, S, G = self.P, self.S, self.G
+        P, G = self.P, self.G
+        S = self.P if self.fp32 else self.S
+        sfx, gemm = self._sfx, self._gemm
         M2, K2 = B * 196, 25 * s.c1
         if self.conv2_implicit:
             # wgrad (+ bias grad) and dgrad as shift-GEMMs; pool2 + ReLU backward (O19, O18) is rebuilt
@@ -382,23 +396,23 @@ class NativeEngine:
                    S["conv2_weight"].data_ptr(), self.dp1.data_ptr(), B)
         else:
             # pool2 + ReLU backward (O19, O18), conv2 bias gradient
-            N.call("mtb_unpool_relu_bwd", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
+            N.call("mtb_unpool_relu_bwd" + sfx, self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
                    self.da2.data_ptr(), B, 14, 14, s.c2)
             da2 = self.da2.view(self.Bmax * 196, s.c2)
-            N.call("mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
+            N.call("mtb_colsum_f32" if self.fp32 else "mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
             # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
-            N.gemm_bf16(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
-                        splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
+            gemm(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
+                 splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
             # conv2 dgrad: dcol = da2 W2^T, then col2im
-            N.gemm_bf16(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
-            N.call("mtb_col2im_5x5", self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
+            gemm(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
+            N.call("mtb_col2im_5x5" + sfx, self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
         # pool1 + ReLU backward fused into the conv1 weight gradient
         if self.conv1_tc:
             wx, _, wstep, wrows = self._win()
             N.call("mtb_conv1_wgrad_tc_win", wx, self.dp1.data_ptr(), self.a1p.data_ptr(),
                    self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, wstep, wrows)
         else:
-            N.call("mtb_conv1_wgrad", self.x_in.data_ptr(), self.dp1.data_ptr(), self.a1p.data_ptr(),
+            N.call("mtb_conv1_wgrad" + sfx, self._win()[0], self.dp1.data_ptr(), self.a1p.data_ptr(),
                    self.idx1.data_ptr(), G["conv1_weight"].data_ptr(), G["conv1_bias"].data_ptr(), B, s.c1)
 
     def _splitk_scratch(self, key: str, M: int, Nn: int, bn: int, splits: int):
@@ -438,12 +452,16 @@ class NativeEngine:
                 a.grads[r], a.params[r], a.shadow[r] = self._grad_ptrs[r], self._param_ptrs[r], self._shadow_ptrs[r]
             if self.has_nvls:
                 a.mc_grads, a.mc_params, a.mc_shadow = self._grad_mc, self._param_mc, self._shadow_mc
+            if self.fp32:                          # no bf16 shadow on the fp32 path
+                for r in range(self.world):
+                    a.shadow[r] = None
+                a.mc_shadow = None
             a.scale = 1.0 / self.world
         else:
             a = N.FusedArgs()
             a.world, a.rank = 1, 0
             a.grads[0], a.params[0], a.shadow[0] = (self.flat_grads.data_ptr(), self.flat_params.data_ptr(),
-                                                    self.shadow.data_ptr())
+                                                    None if self.fp32 else self.shadow.data_ptr())
             a.seq, a.status = self._seq.data_ptr(), self._status.data_ptr()
             a.scale = 1.0
         a.optimizer = _OPT[c.optimizer]

@@ -47,6 +47,17 @@ _SIGS = {
     "mtb_enable_peer_access": [i32],
     "mtb_gemm_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, vp, i32, f32, u64, vp, i32, i32,
                       vp, vp, vp],
+    "mtb_gemm_tf32": [vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, vp, i32, f32, u64, vp, i32, i32, vp, vp, vp],
+    "mtb_conv1_fwd_f32": [vp, vp, vp, vp, vp, i32, i32, vp],
+    "mtb_conv1_wgrad_f32": [vp, vp, vp, vp, vp, vp, i32, i32, vp],
+    "mtb_maxpool2x2_fwd_f32": [vp, vp, vp, i32, i32, i32, i32, vp],
+    "mtb_unpool_relu_bwd_f32": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
+    "mtb_im2col_5x5_f32": [vp, vp, i32, i32, i32, i32, vp],
+    "mtb_col2im_5x5_f32": [vp, vp, i32, i32, i32, i32, vp],
+    "mtb_fc2_softmax_ce_f32": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp],
+    "mtb_fc2_dgrad_f32": [vp, vp, vp, vp, i32, i32, i32, f32, vp],
+    "mtb_fc2_wgrad_f32": [vp, vp, vp, vp, i32, i32, i32, vp],
+    "mtb_colsum_f32": [vp, vp, i64, i32, vp],
     "mtb_init_trunc_normal": [vp, i64, f32, u64, C.c_uint, vp],
     "mtb_fill_f32": [vp, i64, f32, vp],
     "mtb_zero_multi": [vp, vp, i32, vp],
@@ -176,6 +187,17 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, M: int, N: in
     call("mtb_gemm_bf16", ptr(A), ptr(B), ptr(out), M, N, K, int(a_mn), int(b_mn), lda, ldb, ldc,
          int(out.dtype == torch.bfloat16), ptr(bias), int(relu), float(keep_prob), seed, ptr(step_ptr), bn, splits,
          ptr(workspace), ptr(counters))
+
+
+def gemm_tf32(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, a_mn: bool, b_mn: bool,
+              bias: Optional[torch.Tensor] = None, relu: bool = False, keep_prob: float = 1.0, seed: int = 0,
+              step_ptr: Optional[torch.Tensor] = None, bn: int = 0, splits: int = 1,
+              workspace: Optional[torch.Tensor] = None, counters: Optional[torch.Tensor] = None) -> None:
+    """fp32 operands and output, TF32 tensor-core math; same conventions as :func:`gemm_bf16`."""
+    assert A.dtype == torch.float32 and B.dtype == torch.float32 and out.dtype == torch.float32
+    call("mtb_gemm_tf32", ptr(A), ptr(B), ptr(out), M, N, K, int(a_mn), int(b_mn), A.stride(0), B.stride(0),
+         out.stride(0), ptr(bias), int(relu), float(keep_prob), seed, ptr(step_ptr), bn, splits, ptr(workspace),
+         ptr(counters))
 
 
 def gemm_scratch_sizes(M: int, N: int, bn: int, splits: int):
