@@ -42,6 +42,8 @@ struct GemmParams {
   const long long* step_ptr;
   float* workspace;
   unsigned int* counters;
+  int stages;                          // smem ring depth actually used (<= Cfg::kStages): short-K problems take
+                                       // fewer so that several CTAs fit on one SM and their epilogues overlap
 };
 
 template <int BN>
@@ -112,11 +114,11 @@ __device__ __forceinline__ void epilogue_store(const GemmParams& p, const float 
 // then holds 32 elements instead of 64, so a stage covers 32 K and an MN-major atom is 32 elements wide; the
 // byte geometry (16 KB of A per stage, 32 bytes of K per MMA in K-major form) is the same as for bf16.
 template <int BN, bool A_MN, bool B_MN, int CM, int CN, bool TF32 = false>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, TF32 ? 2 : 1)      // fp32 path: two CTAs per SM when the smem ring is short
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const GemmParams p) {
   using C = Cfg<BN>;
-  constexpr int S = C::kStages;
+  const int S = TF32 ? p.stages : C::kStages;        // compile-time for the bf16 instantiations
   constexpr bool kCluster = CM * CN > 1;
   static_assert(!(TF32 && kCluster), "the multicast variants are bf16 only");
   constexpr int kBKe = TF32 ? 32 : 64;             // K elements per stage (one 128-byte row)
@@ -161,8 +163,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 
   if (warp == 0) {
     if (elect_one()) {
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % S, ph = (i / S) & 1;
+      int s = 0, ph = 0;
+      for (int i = 0; i < nkb; ++i, s = (s + 1 == S ? 0 : s + 1), ph ^= (s == 0)) {
         mbar_wait(&empty_bar[s], ph ^ 1);
         mbar_arrive_expect_tx(&full_bar[s], C::kABytes + C::kBBytes);
         const int kc = (kb0 + i) * kBKe;
@@ -352,8 +354,11 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
     attr_set = true;
   }
   dim3 grid((unsigned)mtb::ceil_div(p.M, BM), (unsigned)mtb::ceil_div(p.N, BN), (unsigned)p.splits);
-  MTB_CUDA_CHECK(mtb::launch_cluster(kern, grid, dim3(kThreads), (size_t)Cfg<BN>::kSmemBytes, st, dim3(CM, CN, 1), ma,
-                                     mb, p));
+  GemmParams q = p;
+  q.stages = Cfg<BN>::kStages;
+  if (TF32 && p.kb_per_split < q.stages) q.stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
+  const size_t smem = 1024 + (size_t)q.stages * (Cfg<BN>::kABytes + Cfg<BN>::kBBytes) + 256;
+  MTB_CUDA_CHECK(mtb::launch_cluster(kern, grid, dim3(kThreads), smem, st, dim3(CM, CN, 1), ma, mb, q));
   return 0;
 }
 

@@ -151,9 +151,36 @@ colsum_bf16_kernel(const T* __restrict__ x, float* __restrict__ out, long long R
 // memory and every read of it is a warp-wide broadcast, so the loop is pure FMA.  Loss and error
 // count are reduced inside the block first: one atomic per block instead of one per row.
 constexpr int kHeadWarps = 16;
-template <int NC>
+
+// 8 consecutive activations as floats; 2 consecutive activations in / out (bf16 or fp32 storage)
+__device__ __forceinline__ void load8f(const __nv_bfloat16* p, float (&f)[8]) {
+  const uint4 pk = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) { const float2 t = unpack_bf16x2(w4[e]); f[2 * e] = t.x; f[2 * e + 1] = t.y; }
+}
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ float2 load2f(const __nv_bfloat16* p) {
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+}
+__device__ __forceinline__ float2 load2f(const float* p) { return *reinterpret_cast<const float2*>(p); }
+// returns what was stored (after rounding to the storage type)
+__device__ __forceinline__ float2 store2f(__nv_bfloat16* p, float a, float b) {
+  const __nv_bfloat162 q = __floats2bfloat162_rn(a, b);
+  *reinterpret_cast<__nv_bfloat162*>(p) = q;
+  return __bfloat1622float2(q);
+}
+__device__ __forceinline__ float2 store2f(float* p, float a, float b) {
+  *reinterpret_cast<float2*>(p) = make_float2(a, b);
+  return make_float2(a, b);
+}
+
+template <int NC, class T>
 __global__ void __launch_bounds__(kHeadWarps * 32)
-fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
+fc2_softmax_ce_rows_kernel(const T* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
                            const float* __restrict__ bias, const int* __restrict__ labels, float* __restrict__ logits,
                            float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ loss_accum,
                            int* __restrict__ err_accum, int B, int F, const long long* win_step, long long win_rows) {
@@ -175,20 +202,16 @@ fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __r
 #pragma unroll
   for (int c = 0; c < NC; ++c) acc[c] = 0.f;
   if (row < B) {
-    const uint4* hr = reinterpret_cast<const uint4*>(h + (size_t)row * F + fbeg);
+    const T* hr = h + (size_t)row * F + fbeg;
 #pragma unroll 8
     for (int i = 0; i < fper / 8; ++i) {
-      const uint4 pk = __ldg(hr + i);
-      const uint32_t w4[4] = {pk.x, pk.y, pk.z, pk.w};
+      float hv[8];
+      load8f(hr + i * 8, hv);
       const float* wr = sW + (size_t)(fbeg + i * 8) * NC;
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 hv = unpack_bf16x2(w4[e]);
+      for (int e = 0; e < 8; ++e) {
 #pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          acc[c] = fmaf(hv.x, wr[(2 * e) * NC + c], acc[c]);
-          acc[c] = fmaf(hv.y, wr[(2 * e + 1) * NC + c], acc[c]);
-        }
+        for (int c = 0; c < NC; ++c) acc[c] = fmaf(hv[e], wr[e * NC + c], acc[c]);
       }
     }
   }
@@ -240,10 +263,10 @@ fc2_softmax_ce_rows_kernel(const __nv_bfloat16* __restrict__ h, const float* __r
 // Backward of FC2 in one pass over h: weight gradient, bias gradient, input gradient with the
 // dropout/ReLU mask, and the column sums of that input gradient (= FC1's bias gradient).
 //   grid (F/64, splits), 256 threads: lane <-> 2 features, warps and blockIdx.y split the rows.
-template <int NC>
+template <int NC, class T>
 __global__ void __launch_bounds__(256)
-fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restrict__ dlogits,
-                     const float* __restrict__ W /*[F,NC]*/, __nv_bfloat16* __restrict__ dh, float* __restrict__ dW,
+fc2_bwd_fused_kernel(const T* __restrict__ h, const float* __restrict__ dlogits,
+                     const float* __restrict__ W /*[F,NC]*/, T* __restrict__ dh, float* __restrict__ dW,
                      float* __restrict__ db2, float* __restrict__ db1, int B, int F, float scale, int rows_per_block) {
   extern __shared__ float sm[];                        // dl [rows_per_block][NC], then the reduction buffer
   TRACE2(0);
@@ -268,11 +291,11 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
   if (f0 < F) {
     // 4 rows per pass, their loads issued together (the loop is latency-bound otherwise)
     for (int r0 = warp; r0 < nrows; r0 += 32) {
-      __nv_bfloat162 hq[4];
+      float2 hq[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int r = r0 + 8 * u;
-        if (r < nrows) hq[u] = *reinterpret_cast<const __nv_bfloat162*>(h + (size_t)(b0 + r) * F + f0);
+        if (r < nrows) hq[u] = load2f(h + (size_t)(b0 + r) * F + f0);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -280,7 +303,7 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
         if (r >= nrows) break;
         const float* dl = sdl + r * NC;
         const size_t o = (size_t)(b0 + r) * F + f0;
-        const float2 hv = __bfloat1622float2(hq[u]);
+        const float2 hv = hq[u];
         float t0 = 0.f, t1 = 0.f;
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
@@ -292,9 +315,7 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
         }
         t0 = hv.x > 0.f ? t0 * scale : 0.f;
         t1 = hv.y > 0.f ? t1 * scale : 0.f;
-        const __nv_bfloat162 q = __floats2bfloat162_rn(t0, t1);
-        *reinterpret_cast<__nv_bfloat162*>(dh + o) = q;
-        const float2 qf = __bfloat1622float2(q);         // bias gradient of FC1 sums what FC1's wgrad will see
+        const float2 qf = store2f(dh + o, t0, t1);       // bias gradient of FC1 sums what FC1's wgrad will see
         cs0 += qf.x;
         cs1 += qf.y;
       }
@@ -332,6 +353,42 @@ fc2_bwd_fused_kernel(const __nv_bfloat16* __restrict__ h, const float* __restric
   TRACE2(5);
 }
 
+template <class T>
+int run_head_fast(const T* h, const float* W, const float* bias, const int* labels, float* logits, float* probs,
+                  float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC, const long long* win_step,
+                  long long win_rows, cudaStream_t stream) {
+  MTB_REQUIRE(NC == 10 && F % (8 * kHeadWarps) == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 128");
+  MTB_REQUIRE(win_step == nullptr || win_rows > B, "fc2_softmax_ce_fast: shard must be larger than the batch");
+  const int smem = (F * NC + kHeadWarps * NC * 32) * (int)sizeof(float);
+  MTB_REQUIRE(smem <= 200 * 1024, "fc2_softmax_ce_fast: weight matrix does not fit in shared memory");
+  static int attr_bytes = 0;
+  if (smem > attr_bytes) {
+    MTB_CUDA_CHECK(cudaFuncSetAttribute(fc2_softmax_ce_rows_kernel<10, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_bytes = smem;
+  }
+  MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows_kernel<10, T>, dim3((B + 31) / 32), dim3(kHeadWarps * 32), (size_t)smem,
+                             stream, h, W, bias, labels, logits, probs, dlogits, loss_accum, err_accum, B, F, win_step,
+                             win_rows));
+  return 0;
+}
+
+template <class T>
+int run_bwd_fused(const T* h, const float* dlogits, const float* W, T* dh, float* dW, float* db2, float* db1, int B,
+                  int F, int NC, float scale, cudaStream_t stream) {
+  MTB_REQUIRE(NC == 10 && F % 2 == 0, "fc2_bwd_fused: 10 classes, even F");
+  int splits = 1;
+  const int fx = (F + 63) / 64;
+  // two blocks (16 warps) per SM: the row loop is a dependent FMA chain and needs the extra warps to hide latency
+  while (fx * splits < 256 && B / (splits * 2) >= 32) splits *= 2;
+  const int rows_per_block = (B + splits - 1) / splits;
+  const int smem = (int)sizeof(float) * (rows_per_block * NC > 8 * 22 * 32 ? rows_per_block * NC : 8 * 22 * 32);
+  MTB_REQUIRE(smem <= 48 * 1024, "fc2_bwd_fused: batch slice too large");
+  dim3 grid(fx, splits);
+  MTB_CUDA_CHECK(mtb::launch(fc2_bwd_fused_kernel<10, T>, grid, dim3(256), (size_t)smem, stream, h, dlogits, W, dh, dW,
+                             db2, db1, B, F, scale, rows_per_block));
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -354,37 +411,26 @@ int mtb_fc2_softmax_ce_fast(const void* h_bf16, const float* W, const float* bia
 int mtb_fc2_softmax_ce_fast_win(const void* h_bf16, const float* W, const float* bias, const int* labels,
                                 float* logits, float* probs, float* dlogits, float* loss_accum, int* err_accum, int B,
                                 int F, int NC, const long long* win_step, long long win_rows, cudaStream_t stream) {
-  MTB_REQUIRE(NC == 10 && F % (8 * kHeadWarps) == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 128");
-  MTB_REQUIRE(win_step == nullptr || win_rows > B, "fc2_softmax_ce_fast: shard must be larger than the batch");
-  const int smem = (F * NC + kHeadWarps * NC * 32) * (int)sizeof(float);
-  MTB_REQUIRE(smem <= 200 * 1024, "fc2_softmax_ce_fast: weight matrix does not fit in shared memory");
-  static int attr_bytes = 0;
-  if (smem > attr_bytes) {
-    MTB_CUDA_CHECK(cudaFuncSetAttribute(fc2_softmax_ce_rows_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_bytes = smem;
-  }
-  MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows_kernel<10>, dim3((B + 31) / 32), dim3(kHeadWarps * 32), (size_t)smem, stream,
-                             reinterpret_cast<const __nv_bfloat16*>(h_bf16), W, bias, labels, logits, probs, dlogits,
-                             loss_accum, err_accum, B, F, win_step, win_rows));
-  return 0;
+  return run_head_fast(reinterpret_cast<const __nv_bfloat16*>(h_bf16), W, bias, labels, logits, probs, dlogits,
+                       loss_accum, err_accum, B, F, NC, win_step, win_rows, stream);
+}
+int mtb_fc2_softmax_ce_fast_win_f32(const float* h, const float* W, const float* bias, const int* labels,
+                                    float* logits, float* probs, float* dlogits, float* loss_accum, int* err_accum,
+                                    int B, int F, int NC, const long long* win_step, long long win_rows,
+                                    cudaStream_t stream) {
+  return run_head_fast(h, W, bias, labels, logits, probs, dlogits, loss_accum, err_accum, B, F, NC, win_step, win_rows,
+                       stream);
 }
 
 // dW, db2 and db1 are accumulated into; dh is overwritten.  NC must be 10.
 int mtb_fc2_bwd_fused(const void* h_bf16, const float* dlogits, const float* W, void* dh_bf16, float* dW, float* db2,
                       float* db1, int B, int F, int NC, float scale, cudaStream_t stream) {
-  MTB_REQUIRE(NC == 10 && F % 2 == 0, "fc2_bwd_fused: 10 classes, even F");
-  int splits = 1;
-  const int fx = (F + 63) / 64;
-  // two blocks (16 warps) per SM: the row loop is a dependent FMA chain and needs the extra warps to hide latency
-  while (fx * splits < 256 && B / (splits * 2) >= 32) splits *= 2;
-  const int rows_per_block = (B + splits - 1) / splits;
-  const int smem = (int)sizeof(float) * (rows_per_block * NC > 8 * 22 * 32 ? rows_per_block * NC : 8 * 22 * 32);
-  MTB_REQUIRE(smem <= 48 * 1024, "fc2_bwd_fused: batch slice too large");
-  dim3 grid(fx, splits);
-  MTB_CUDA_CHECK(mtb::launch(fc2_bwd_fused_kernel<10>, grid, dim3(256), (size_t)smem, stream,
-                             reinterpret_cast<const __nv_bfloat16*>(h_bf16), dlogits, W,
-                             reinterpret_cast<__nv_bfloat16*>(dh_bf16), dW, db2, db1, B, F, scale, rows_per_block));
-  return 0;
+  return run_bwd_fused(reinterpret_cast<const __nv_bfloat16*>(h_bf16), dlogits, W,
+                       reinterpret_cast<__nv_bfloat16*>(dh_bf16), dW, db2, db1, B, F, NC, scale, stream);
+}
+int mtb_fc2_bwd_fused_f32(const float* h, const float* dlogits, const float* W, float* dh, float* dW, float* db2,
+                          float* db1, int B, int F, int NC, float scale, cudaStream_t stream) {
+  return run_bwd_fused(h, dlogits, W, dh, dW, db2, db1, B, F, NC, scale, stream);
 }
 
 int mtb_fc2_softmax_ce(const void* h_bf16, const float* W, const float* bias, const int* labels, float* logits,

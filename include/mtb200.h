@@ -166,6 +166,12 @@ int mtb_fc2_dgrad_f32(const float* dlogits, const float* W, const float* h, floa
 int mtb_fc2_wgrad_f32(const float* h, const float* dlogits, float* dW, float* db, int B, int F, int NC,
                       cudaStream_t stream);
 int mtb_colsum_f32(const float* x, float* out, long long R, int C, cudaStream_t stream);
+int mtb_fc2_softmax_ce_fast_win_f32(const float* h, const float* W, const float* bias, const int* labels,
+                                    float* logits, float* probs, float* dlogits, float* loss_accum, int* err_accum,
+                                    int B, int F, int NC, const long long* win_step, long long win_rows,
+                                    cudaStream_t stream);
+int mtb_fc2_bwd_fused_f32(const float* h, const float* dlogits, const float* W, float* dh, float* dW, float* db2,
+                          float* db1, int B, int F, int NC, float scale, cudaStream_t stream);
 
 /* ---- K1: fused cross-GPU allreduce + average + L2 + optimizer + LR schedule + bf16 cast
  *      (Gather/mean/assign mpipy.py:121-152; l2 mpipy.py:57-58; lr mpipy.py:60-64; momentum mpipy.py:65) */

@@ -141,7 +141,7 @@ class NativeEngine:
         self.dp1 = z(Bmax, 14, 14, s.c1)
         # conv1 on tensor cores when it has 32 output channels, else the CUDA-core kernel
         self.conv1_tc = s.c1 == 32 and self.conv_impl != "im2col" and not self.fp32
-        self._fast_head = s.num_classes == 10 and s.fc % 128 == 0 and s.fc * 40 <= 170 * 1024 and not self.fp32
+        self._fast_head = s.num_classes == 10 and s.fc % 128 == 0 and s.fc * 40 <= 170 * 1024
         # the generic layer kernels exist for both activation types; GEMMs are bf16 or TF32
         self._sfx = "_f32" if self.fp32 else ""
         self._gemm = N.gemm_tf32 if self.fp32 else N.gemm_bf16
@@ -324,9 +324,10 @@ class NativeEngine:
         flat = self.a2p.view(self.Bmax, s.flat_dim)
         bn, splits = 64 if B * s.fc < 96 * 128 * 128 else 128, 1
         tiles = -(-B // 128) * -(-s.fc // bn)
-        if tiles < 64 and os.environ.get("MTB_FC_SPLITK") == "1":
-            # small batch: split K so the GEMM covers the chip.  Measured slower at batch 100 (the
-            # last-arriver reduction costs more than the idle SMs), so opt-in only.
+        if tiles < 64 and (self.fp32 or os.environ.get("MTB_FC_SPLITK") == "1"):
+            # small batch: split K so the GEMM covers the chip.  With bf16 weights it measured slower at
+            # batch 100 (the last-arriver reduction costs more than the idle SMs), so opt-in only; with
+            # fp32 weights 16 CTAs stream 12.8 MB at 0.46 TB/s (28 us) and the split pays.
             splits = max(1, min(8, 128 // tiles))
         ws, cnt = self._splitk_scratch("fc1_fprop", B, s.fc, bn, splits)
         gemm(flat, S["fc1_weight"], self.h, B, s.fc, s.flat_dim, False, True, bias=P["fc1_bias"], relu=True,
@@ -337,7 +338,7 @@ class NativeEngine:
                 self.dlogits.data_ptr() if with_loss else None, self.loss_acc.data_ptr() if with_loss else None,
                 self.err_acc.data_ptr() if with_loss else None, B, s.fc, s.num_classes)
         if self._fast_head:
-            N.call("mtb_fc2_softmax_ce_fast_win", *head, wstep, wrows)
+            N.call("mtb_fc2_softmax_ce_fast_win" + sfx, *head, wstep, wrows)
         else:
             N.call("mtb_fc2_softmax_ce" + sfx, *head)
 
@@ -356,9 +357,9 @@ class NativeEngine:
         scale = 1.0 / s.keep_prob if c.dropout else 1.0
         M2, K2 = B * 196, 25 * s.c1
         flat = self.a2p.view(self.Bmax, s.flat_dim)
-        if s.num_classes == 10 and not self.fp32:
+        if s.num_classes == 10:
             # dW2, db2, dh (with the dropout / ReLU mask) and db of FC1 in one pass over h
-            N.call("mtb_fc2_bwd_fused", self.h.data_ptr(), self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(),
+            N.call("mtb_fc2_bwd_fused" + sfx, self.h.data_ptr(), self.dlogits.data_ptr(), P["fc2_weight"].data_ptr(),
                    self.dh.data_ptr(), G["fc2_weight"].data_ptr(), G["fc2_bias"].data_ptr(),
                    G["fc1_bias"].data_ptr(), B, s.fc, s.num_classes, scale)
         else:

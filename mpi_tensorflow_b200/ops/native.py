@@ -58,6 +58,8 @@ _SIGS = {
     "mtb_fc2_dgrad_f32": [vp, vp, vp, vp, i32, i32, i32, f32, vp],
     "mtb_fc2_wgrad_f32": [vp, vp, vp, vp, i32, i32, i32, vp],
     "mtb_colsum_f32": [vp, vp, i64, i32, vp],
+    "mtb_fc2_softmax_ce_fast_win_f32": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, i64, vp],
+    "mtb_fc2_bwd_fused_f32": [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, vp],
     "mtb_init_trunc_normal": [vp, i64, f32, u64, C.c_uint, vp],
     "mtb_fill_f32": [vp, i64, f32, vp],
     "mtb_zero_multi": [vp, vp, i32, vp],

@@ -161,6 +161,19 @@ def test_fp32_conv1_and_head_twins(N, dev):
     assert _rel(dh.cpu(), (rdl @ W.cpu().t()) * (h.cpu() > 0).float() * 2.0) < 1e-5
     assert _rel(dW2.cpu(), h.cpu().t() @ rdl) < 1e-4 and _rel(db2.cpu(), rdl.sum(0)) < 1e-4
     assert _rel(cs.cpu(), dh.cpu().sum(0)) < 1e-4
+    # the engine's variants: weights in shared memory, one fused backward pass
+    l2, p2, d2 = (torch.zeros(B, NC, device=dev) for _ in range(3))
+    loss2, err2 = torch.zeros(1, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)
+    N.call("mtb_fc2_softmax_ce_fast_win_f32", h.data_ptr(), W.data_ptr(), b2.data_ptr(), y.data_ptr(), l2.data_ptr(),
+           p2.data_ptr(), d2.data_ptr(), loss2.data_ptr(), err2.data_ptr(), B, F, NC, None, 0)
+    dh2 = torch.zeros(B, F, device=dev)
+    dW3, db3, db1 = torch.zeros(F, NC, device=dev), torch.zeros(NC, device=dev), torch.zeros(F, device=dev)
+    N.call("mtb_fc2_bwd_fused_f32", h.data_ptr(), dl.data_ptr(), W.data_ptr(), dh2.data_ptr(), dW3.data_ptr(),
+           db3.data_ptr(), db1.data_ptr(), B, F, NC, 2.0)
+    torch.cuda.synchronize()
+    assert torch.allclose(l2, logits, atol=1e-4, rtol=1e-4) and torch.allclose(d2, dl, atol=1e-7, rtol=1e-3)
+    assert abs(float(loss2) - float(loss)) < 1e-4 and int(err2) == int(err)
+    assert _rel(dh2, dh) < 1e-5 and _rel(dW3, dW2) < 1e-4 and _rel(db3, db2) < 1e-4 and _rel(db1, cs) < 1e-4
 
 
 def _shards(n_rows, seed=0):
@@ -194,7 +207,7 @@ def test_fp32_step_matches_fp32_oracle(model, batch, dropout):
         r = rg[p.key].reshape(-1)
         rels[p.key] = float((g - r).norm() / (r.norm() + 1e-12))
     # TF32 drops 13 mantissa bits of every MMA operand; the conv1 gradient sits 4 such products deep
-    bad = {k: v for k, v in rels.items() if v > (2e-2 if k.startswith("conv") else 5e-3)}
+    bad = {k: v for k, v in rels.items() if v > (2e-2 if k.startswith("conv") else 1e-2)}
     assert not bad, f"{bad} (all: {rels})"
 
 
