@@ -18,8 +18,8 @@ from typing import Optional
 class TrainConfig:
     # model
     model: str = "tutorial512"          # tutorial512 | official1024 | wide
-    dtype: str = "bf16"                 # GPU compute: bf16 tensor-core operands, fp32 accumulate / master / optimizer.
-                                        # "fp32" is accepted for the CPU engine; the GPU engine warns and runs bf16.
+    dtype: str = "bf16"                 # bf16: bf16 tensor-core operands, fp32 accumulate / master / optimizer.
+                                        # fp32: fp32 storage everywhere, TF32 tensor-core GEMMs, fp32 CUDA-core conv1/head.
     seed: int = 1                       # mpipy.py:40
     # data
     data: str = "synthetic"             # synthetic | mnist

@@ -123,6 +123,21 @@ def train(comm, outdir):
     if comm.rank == 0:
         with open(os.path.join(outdir, "result.json"), "w") as f:
             json.dump({k: v for k, v in res.items() if k != "phases_ms"}, f)
+    tr.close()
+    comm.barrier()
+    # the fp32 / TF32 path over the same fused allreduce (full fp32 parameter broadcast, no bf16 shadow)
+    cfg32 = TrainConfig(model="official1024", batch=100, dtype="fp32", max_steps=12, eval_every=0, log_every=0,
+                        dropout=True, step_timeout_s=60, lr=0.02)
+    tr = Trainer(cfg32, comm)
+    tr.load_data()
+    losses = [tr.step() for _ in range(12)]
+    tr.engine.sync_state()
+    comm.check_status()
+    mine = tr.engine.flat_params.clone()
+    ref = mine.clone()
+    comm.bcast(ref, root=0)
+    assert torch.equal(mine, ref), "fp32 replicas diverged"
+    assert np.isfinite(losses).all() and losses[-1] < losses[0], losses
     print(f"GPU_TRAIN_OK rank {comm.rank}/{comm.size}", flush=True)
     tr.close()
 
