@@ -43,6 +43,7 @@ def timed(fn, comm, iters):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=int, default=1024)
+    ap.add_argument("--min-bytes", type=int, default=4096, help="first message size of the sweep (x4 steps)")
     ap.add_argument("--out", default=None)
     ap.add_argument("--no-nccl", action="store_true")
     a = ap.parse_args()
@@ -65,7 +66,7 @@ def main():
             if r == 0:
                 print(f"# nccl unavailable: {e}", flush=True)
     rows = []
-    size = 4096
+    size = max(4096, a.min_bytes)
     while size <= a.max_mb << 20:
         elems = size // 4
         iters = 200 if size <= (1 << 20) else (50 if size <= (64 << 20) else 10)
