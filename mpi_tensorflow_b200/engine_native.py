@@ -498,7 +498,8 @@ class NativeEngine:
         # it has nothing to save and the plain two-shot is faster
         if count * 4 <= (256 << 10):
             return 0
-        return 2 if (self.has_nvls and self.world >= 4) else 1
+        # NVLS loses to the plain two-shot again at 1 GB (3.40 vs 2.95 ms, profiles/late_n8/sweep_1gb.jsonl)
+        return 2 if (self.has_nvls and self.world >= 4 and count * 4 <= (512 << 20)) else 1
 
     def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
                 advance: bool = True, grid: int = 0):
