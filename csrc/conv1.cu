@@ -27,11 +27,14 @@ __device__ __forceinline__ void load_padded_image(float* s_img, const float* __r
 template <class T>
 __global__ void __launch_bounds__(256)
 conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25,C1]*/, const float* __restrict__ bias,
-                 T* __restrict__ out, uint8_t* __restrict__ idx, int B, int C1) {
+                 T* __restrict__ out, uint8_t* __restrict__ idx, int B, int C1, int parts) {
   __shared__ float s_img[PW * PW];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int groups = C1 / 32;
-  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+  // small batches: `parts` blocks share an image (each takes a slice of the pooled pixels) so the grid covers the chip
+  const int part = blockIdx.x % parts, per = (POOLED * POOLED + parts - 1) / parts;
+  const int item0 = part * per, item1 = min(POOLED * POOLED, item0 + per);
+  for (int b = blockIdx.x / parts; b < B; b += gridDim.x / parts) {
     __syncthreads();
     load_padded_image(s_img, x + (size_t)b * IMG * IMG);
     __syncthreads();
@@ -41,7 +44,7 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25,
 #pragma unroll
       for (int t = 0; t < 25; ++t) wt[t] = __ldg(w + t * C1 + c);
       const float bs = __ldg(bias + c);
-      for (int item = warp; item < POOLED * POOLED; item += nwarps) {
+      for (int item = item0 + warp; item < item1; item += nwarps) {
         const int pi = item / POOLED, pj = item % POOLED;
         const float* p = s_img + (2 * pi) * PW + 2 * pj;     // top-left of the 6x6 patch (padded coords)
         float a00 = bs, a01 = bs, a10 = bs, a11 = bs;
@@ -74,22 +77,24 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w /*[25,
 template <class T>
 __global__ void __launch_bounds__(256)
 conv1_wgrad_kernel(const float* __restrict__ x, const T* __restrict__ dP, const T* __restrict__ P, const uint8_t* __restrict__ idx, float* __restrict__ dW,
-                   float* __restrict__ db, int B, int C1) {
+                   float* __restrict__ db, int B, int C1, int parts) {
   __shared__ float s_img[PW * PW];
   __shared__ float s_red[8][26][33];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int groups = C1 / 32;
+  const int part = blockIdx.x % parts, per = (POOLED * POOLED + parts - 1) / parts;
+  const int item0 = part * per, item1 = min(POOLED * POOLED, item0 + per);
   for (int g = 0; g < groups; ++g) {
     const int c = g * 32 + lane;
     float acc[25];
 #pragma unroll
     for (int t = 0; t < 25; ++t) acc[t] = 0.f;
     float accb = 0.f;
-    for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    for (int b = blockIdx.x / parts; b < B; b += gridDim.x / parts) {
       __syncthreads();
       load_padded_image(s_img, x + (size_t)b * IMG * IMG);
       __syncthreads();
-      for (int item = warp; item < POOLED * POOLED; item += nwarps) {
+      for (int item = item0 + warp; item < item1; item += nwarps) {
         const int pi = item / POOLED, pj = item % POOLED;
         const size_t o = (((size_t)b * POOLED + pi) * POOLED + pj) * C1 + c;
         float gv = ldf(dP + o);
@@ -126,6 +131,15 @@ conv1_wgrad_kernel(const float* __restrict__ x, const T* __restrict__ dP, const 
   }
 }
 
+// grid = parts * (images in flight): up to `cap` blocks; when the batch alone cannot fill it, 2 or 4 blocks per image
+inline void conv1_grid(int B, int cap, int* parts, int* grid) {
+  int p = 1;
+  while (p < 4 && B * p * 2 <= cap) p *= 2;
+  int imgs = B * p <= cap ? B : cap / p;
+  *parts = p;
+  *grid = imgs * p;
+}
+
 }  // namespace
 
 extern "C" {
@@ -133,8 +147,9 @@ extern "C" {
 int mtb_conv1_fwd(const float* x, const float* w, const float* bias, void* out_bf16, uint8_t* idx, int B, int C1,
                   cudaStream_t stream) {
   MTB_REQUIRE(C1 % 32 == 0 && B > 0, "conv1_fwd: C1 must be a multiple of 32");
-  int grid = B < 148 * 4 ? B : 148 * 4;
-  conv1_fwd_kernel<<<grid, 256, 0, stream>>>(x, w, bias, reinterpret_cast<__nv_bfloat16*>(out_bf16), idx, B, C1);
+  int parts, grid;
+  conv1_grid(B, 148 * 4, &parts, &grid);
+  conv1_fwd_kernel<<<grid, 256, 0, stream>>>(x, w, bias, reinterpret_cast<__nv_bfloat16*>(out_bf16), idx, B, C1, parts);
   MTB_LAUNCH_CHECK();
   return 0;
 }
@@ -142,8 +157,9 @@ int mtb_conv1_fwd(const float* x, const float* w, const float* bias, void* out_b
 int mtb_conv1_fwd_f32(const float* x, const float* w, const float* bias, float* out, uint8_t* idx, int B, int C1,
                       cudaStream_t stream) {
   MTB_REQUIRE(C1 % 32 == 0 && B > 0, "conv1_fwd: C1 must be a multiple of 32");
-  int grid = B < 148 * 4 ? B : 148 * 4;
-  conv1_fwd_kernel<<<grid, 256, 0, stream>>>(x, w, bias, out, idx, B, C1);
+  int parts, grid;
+  conv1_grid(B, 148 * 4, &parts, &grid);
+  conv1_fwd_kernel<<<grid, 256, 0, stream>>>(x, w, bias, out, idx, B, C1, parts);
   MTB_LAUNCH_CHECK();
   return 0;
 }
@@ -152,9 +168,11 @@ int mtb_conv1_fwd_f32(const float* x, const float* w, const float* bias, float* 
 int mtb_conv1_wgrad(const float* x, const void* dP_bf16, const void* P_bf16, const uint8_t* idx, float* dW, float* db,
                     int B, int C1, cudaStream_t stream) {
   MTB_REQUIRE(C1 % 32 == 0 && B > 0, "conv1_wgrad: C1 must be a multiple of 32");
-  int grid = B < 148 * 2 ? B : 148 * 2;
+  int parts, grid;
+  conv1_grid(B, 148 * 2, &parts, &grid);
   conv1_wgrad_kernel<<<grid, 256, 0, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(dP_bf16),
-                                               reinterpret_cast<const __nv_bfloat16*>(P_bf16), idx, dW, db, B, C1);
+                                               reinterpret_cast<const __nv_bfloat16*>(P_bf16), idx, dW, db, B, C1,
+                                               parts);
   MTB_LAUNCH_CHECK();
   return 0;
 }
@@ -162,8 +180,9 @@ int mtb_conv1_wgrad(const float* x, const void* dP_bf16, const void* P_bf16, con
 int mtb_conv1_wgrad_f32(const float* x, const float* dP, const float* P, const uint8_t* idx, float* dW, float* db,
                         int B, int C1, cudaStream_t stream) {
   MTB_REQUIRE(C1 % 32 == 0 && B > 0, "conv1_wgrad: C1 must be a multiple of 32");
-  int grid = B < 148 * 2 ? B : 148 * 2;
-  conv1_wgrad_kernel<<<grid, 256, 0, stream>>>(x, dP, P, idx, dW, db, B, C1);
+  int parts, grid;
+  conv1_grid(B, 148 * 2, &parts, &grid);
+  conv1_wgrad_kernel<<<grid, 256, 0, stream>>>(x, dP, P, idx, dW, db, B, C1, parts);
   MTB_LAUNCH_CHECK();
   return 0;
 }
