@@ -247,6 +247,7 @@ class NativeEngine:
         self.opt_step = step
         self.params_changed()
         self.synchronize()
+        self._mail.zero_()                        # a rewound counter must not match losses mailed before
 
     # ------------------------------------------------------------------ data
     def attach_dataset(self, shards):
@@ -556,10 +557,11 @@ class NativeEngine:
 
     _MAIL_RING = 16
 
-    def _await_loss(self, step_no: int, timeout: float = 60.0) -> float:
+    def _await_loss(self, step_no: int, timeout: Optional[float] = None) -> float:
         """Loss of optimizer step ``step_no`` (1-based value of the device counter after it), read
         from the pinned mailbox K1 writes: no copy, no stream synchronize, just a poll."""
         slot, want = (step_no - 1) % self._MAIL_RING, step_no & 0xFFFFFFFF
+        timeout = float(self.cfg.step_timeout_s) if timeout is None else timeout
         mail, t0, spins = self._mail_np, None, 0
         while True:
             word = int(mail[slot])

@@ -13,6 +13,7 @@ Run ``python -m mpi_tensorflow_b200.ops.build`` (add ``--force`` to rebuild).
 from __future__ import annotations
 
 import hashlib
+import shlex
 import os
 import shutil
 import subprocess
@@ -41,6 +42,7 @@ NVCC_FLAGS = [
     f"-I{INCLUDE}", f"-I{CSRC}",
 ]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread", f"-I{INCLUDE}"]
+CXX_FLAGS += shlex.split(os.environ.get("CXXFLAGS", ""))       # e.g. -fsanitize=address,undefined (scripts/sanitize.sh)
 
 
 def _digest(paths: List[Path], extra: str) -> str:

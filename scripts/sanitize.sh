@@ -4,7 +4,7 @@
 #   gpurun --timeout 900 -- 'bash scripts/sanitize.sh memcheck  "conv2 and 3"'
 #   gpurun --timeout 900 -- 'bash scripts/sanitize.sh racecheck "fc2"'
 #   gpurun --timeout 900 -- 'bash scripts/sanitize.sh synccheck "maxpool"'
-# The host-side C++ (csrc/host) has its own target:  CXXFLAGS=-fsanitize=address,undefined python -m mpi_tensorflow_b200.ops.build --host --force
+# The host-side C++ (csrc/host) has its own target: bash scripts/asan_host.sh (ASan + UBSan under the CPU test suite).
 set -euo pipefail
 tool=${1:-memcheck}
 sel=${2:-"maxpool or im2col"}

@@ -137,3 +137,11 @@ def test_loss_mailbox_matches_device_accumulator():
         assert mailed == pytest.approx(float(eng.loss_acc.item()), rel=0, abs=0)
     with pytest.raises(RuntimeError):
         eng._await_loss(eng.opt_step + 1, timeout=0.2)      # a step that never ran
+    # rewinding the step counter (checkpoint restore) must not match losses mailed before the rewind
+    params, slots = eng.get_params(), eng.get_slots()
+    eng.set_state(params, slots, 3)
+    tr.global_step = 3
+    for i in range(4, 8):
+        mailed = tr.step()
+        torch.cuda.synchronize()
+        assert eng.opt_step == i and mailed == float(eng.loss_acc.item())
