@@ -236,3 +236,31 @@ def test_fault_injection_mid_training(monkeypatch):
     from mpi_tensorflow_b200.utils.faults import InjectedFault
     with pytest.raises((InjectedFault, CommError)):
         FakeWorld(2, timeout=2.0).run(body)
+
+
+def test_loss_mailbox_decoding_without_a_gpu():
+    """The host side of the loss mailbox (engine_native.NativeEngine._await_loss): one 8-byte word
+    carries {step number : fp32 loss}; a stale or missing word must time out, never be returned."""
+    import struct
+    import types
+
+    from mpi_tensorflow_b200.engine_native import NativeEngine
+
+    ring = NativeEngine._MAIL_RING
+    mail = np.zeros(ring, dtype=np.int64)
+    eng = types.SimpleNamespace(_mail_np=mail, _MAIL_RING=ring, cfg=types.SimpleNamespace(step_timeout_s=0.2))
+
+    def post(step, loss):
+        bits = struct.unpack("<I", struct.pack("<f", loss))[0]
+        mail[(step - 1) % ring] = np.array([(step << 32) | bits], dtype=np.uint64).view(np.int64)[0]
+
+    post(5, 1.25)
+    assert NativeEngine._await_loss(eng, 5) == 1.25
+    post(5 + ring, -3.5)                                       # the slot is reused one ring later
+    assert NativeEngine._await_loss(eng, 5 + ring) == -3.5
+    with pytest.raises(RuntimeError):
+        NativeEngine._await_loss(eng, 5)                       # overwritten: the old step can no longer be read
+    with pytest.raises(RuntimeError):
+        NativeEngine._await_loss(eng, 6, timeout=0.05)         # never mailed
+    post(2 ** 31 + 7, 0.5)                                     # step numbers with the top bit set decode too
+    assert NativeEngine._await_loss(eng, 2 ** 31 + 7) == 0.5
