@@ -59,6 +59,8 @@ def parse():
     ap.add_argument("--overlap", action="store_true", help="fc-bucket K1 on a comm stream under the conv backward")
     ap.add_argument("--no-overlap", action="store_true", help="(default) one K1 launch at the end of the step")
     ap.add_argument("--dtype", default="bf16")
+    ap.add_argument("--fuse-wgrad-rs", action="store_true",
+                    help="FC1 weight gradient: GEMM -> reduce-scatter in one kernel over peer memory (N > 1)")
     return ap.parse_args()
 
 
@@ -172,7 +174,7 @@ def run_ours(args) -> dict:
     B, K, W = args.batch, args.steps, args.warmup
     cfg = TrainConfig(model=args.model, batch=B, dtype=args.dtype, optimizer=args.optimizer, eval_every=0,
                       log_every=0, dropout=True, cuda_graph=not args.no_graph, comm_algo=args.comm_algo,
-                      overlap=args.overlap and not args.no_overlap,
+                      overlap=args.overlap and not args.no_overlap, fuse_wgrad_rs=args.fuse_wgrad_rs,
                       lr=0.01 if args.optimizer != "adam" else 1e-4)
     tr = Trainer(cfg, comm)
     eng = tr.engine
@@ -246,7 +248,8 @@ def run_ours(args) -> dict:
         "config": {"model": f"mnist_cnn_{args.model}", "global_batch": n * B, "per_rank_batch": B, "seq_len": 784,
                    "parallelism": f"dp{n}", "optimizer": args.optimizer, "cuda_graph": cfg.cuda_graph,
                    "l2": "inputs larger than L2: 172 MB per-rank shard streamed sequentially, no flush",
-                   "comm": "fused P2P allreduce+update kernel" if n > 1 else "fused update kernel",
+                   "comm": ("fused P2P allreduce+update kernel" if n > 1 else "fused update kernel")
+                           + (" + FC1 wgrad GEMM with reduce-scatter epilogue" if getattr(eng, "_rs_mode", False) else ""),
                    "math": ("fp32 storage and accumulation, TF32 tensor-core operands (kind::tf32), fp32 CUDA cores for "
                             "conv1 and the loss head") if args.dtype == "fp32" else
                            "bf16 tensor-core operands, fp32 accumulation, fp32 master weights and optimizer",

@@ -62,6 +62,11 @@ struct FusedParams {
   long long shard_begin[4], shard_end[4];
   long long* advance_step;                          // bumped by the last block to finish (may be null)
   unsigned int* done_counter;
+  // Ranges whose gradient slices arrive ALREADY summed in the owner's buffer: the producing GEMM's epilogue
+  // added every rank's tile straight into the owner over NVLink (mtb_gemm_bf16_rs).  The owner reads its slice
+  // locally, skips the peer reduction, and clears it for the next step.
+  int n_prered;
+  long long prered_begin[2], prered_end[2];
   const float* loss_src;                            // step result mailed to the host by the last block (may be null)
   unsigned long long* loss_mail;                    // pinned host ring of {f32 loss, u32 step} words
   int loss_ring;
@@ -159,6 +164,14 @@ __device__ __forceinline__ bool master_sharded(const FusedParams& p, long long i
   return s;
 }
 
+__device__ __forceinline__ bool prereduced(const FusedParams& p, long long i) {
+  bool s = false;
+#pragma unroll
+  for (int r = 0; r < 2; ++r)
+    if (r < p.n_prered && i >= p.prered_begin[r] && i < p.prered_end[r]) s = true;
+  return s;
+}
+
 // One float4 of the optimizer.  g is the already averaged gradient.
 __device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g) {
   float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
@@ -212,6 +225,9 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
         const long long i = p.offset + (v << 2);
         if (KIND == kLocal) {
           g[u] = *reinterpret_cast<const float4*>(p.grads[0] + i);
+        } else if ((KIND == kNvls || KIND == kTwoShot) && p.n_prered > 0 && prereduced(p, i)) {
+          g[u] = ld_peer_f4(p.grads[p.rank] + i);            // summed in place by the producers' epilogues
+          *reinterpret_cast<float4*>(const_cast<float*>(p.grads[p.rank]) + i) = make_float4(0.f, 0.f, 0.f, 0.f);
         } else if (KIND == kNvls) {
           g[u] = multimem_ld_reduce_f4(p.mc_grads + i);
         } else {
@@ -260,7 +276,9 @@ fused_allreduce_update_kernel(const FusedParams p) {
   const uint32_t seq = s_seq;
   const Hyper h = make_hyper(p);
   const bool multi = p.world > 1;
-  if (multi) cross_gpu_barrier(p, b, seq + 1, false);   // every peer's gradients are complete
+  // every peer's gradients are complete (with pre-reduced ranges some of them were written into MY memory by
+  // peers' kernels: the fence makes this rank's own remote additions globally visible before it signals)
+  if (multi) cross_gpu_barrier(p, b, seq + 1, p.n_prered > 0);
 
   const long long vec_total = p.count >> 2;
   if (!multi) {
@@ -347,6 +365,11 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->advance_step = reinterpret_cast<long long*>(a->advance_step);
   p->done_counter = reinterpret_cast<unsigned int*>(a->done_counter);
   MTB_REQUIRE(p->advance_step == nullptr || p->done_counter != nullptr, "fused: advance_step needs done_counter");
+  MTB_REQUIRE(a->n_prered >= 0 && a->n_prered <= 2, "fused: at most 2 pre-reduced ranges");
+  MTB_REQUIRE(a->n_prered == 0 || (a->world > 1 && a->algo != 0),
+              "fused: pre-reduced ranges need an owner-sliced algorithm (two-shot or nvls) and peers");
+  p->n_prered = a->n_prered;
+  for (int r = 0; r < 2; ++r) { p->prered_begin[r] = a->prered_begin[r]; p->prered_end[r] = a->prered_end[r]; }
   p->loss_src = reinterpret_cast<const float*>(a->loss_src);
   p->loss_mail = reinterpret_cast<unsigned long long*>(a->loss_mail);
   p->loss_ring = a->loss_ring;

@@ -47,6 +47,17 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
                   long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
                   float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
                   void* workspace, void* counters, cudaStream_t stream);
+/* GEMM -> reduce-scatter in ONE kernel: the product is added (red.v4.f32 over NVLink) into the flat gradient buffer of
+ * whichever rank owns each 16-byte vector, so the cross-GPU reduction of this gradient overlaps the multiplication tile
+ * by tile and mtb_fused_allreduce_update (prered_* ranges) skips it.  Slice r = elements [r*per, (r+1)*per). */
+typedef struct {
+  int world, rank;
+  long long base;       /* flat element offset of the product's element (0,0) */
+  long long per;        /* elements per owner slice, multiple of 4 (same partition as the two-shot / nvls update) */
+  void* out[16];        /* every rank's flat fp32 gradient buffer, peer-mapped */
+} mtb_gemm_rs;
+int mtb_gemm_bf16_rs(const void* A, const void* B, int M, int N, int K, int a_mn_major, int b_mn_major, long long lda,
+                     long long ldb, long long ldc, int bn, const mtb_gemm_rs* rs, cudaStream_t stream);
 /* fp32 operands and output, TF32 tensor-core math (kind::tf32), fp32 accumulation: the fp32 training path. */
 int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int K, int a_mn_major, int b_mn_major,
                   long long lda, long long ldb, long long ldc, const float* bias, int relu, float keep_prob,
@@ -210,6 +221,11 @@ typedef struct mtb_fused_args {
   const void* loss_src;
   void* loss_mail;
   int loss_ring;        /* power of two */
+  /* Pre-reduced ranges (two-shot / nvls, world > 1): element ranges of the gradient buffer whose owner slices already
+   * hold the sum over ranks because the producing GEMM added its tiles into the owners directly (mtb_gemm_bf16_rs).
+   * The owner reads them locally instead of reducing over peers and zeroes them for the next step. */
+  int n_prered;
+  long long prered_begin[2], prered_end[2];
 } mtb_fused_args;
 int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
 int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */

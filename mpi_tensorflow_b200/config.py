@@ -47,6 +47,8 @@ class TrainConfig:
     sync_include_momentum: bool = False
     sync_root_only: bool = False        # True reproduces mpipy.py:129 (mean stays on root)
     comm_algo: str = "auto"             # auto | oneshot | twoshot | nvls | nccl (baseline)
+    fuse_wgrad_rs: bool = False         # FC1 weight gradient: GEMM -> reduce-scatter in one kernel (tiles added into the
+                                        # owner rank's slice over NVLink); K1 then skips that range's peer reduction
     comm_dtype: str = "fp32"            # gradient wire format; only fp32 is implemented (bf16 is rejected)
     shard_master: bool = True           # two-shot / nvls: the big weights' fp32 master stays with the slice owner,
                                         # only their bf16 shadow is broadcast (gathered on demand for checkpoints)

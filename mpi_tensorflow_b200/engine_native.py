@@ -60,6 +60,19 @@ class NativeEngine:
             raise ValueError("NativeEngine supports 28x28 inputs, c1 % 32 == 0, c2 % 8 == 0, fc % 8 == 0")
         self._alloc_state()
         self._alloc_activations(max(self.B, cfg.eval_batch))
+        # GEMM -> reduce-scatter for the FC1 weight gradient (cfg.fuse_wgrad_rs): needs peers, an owner-sliced K1
+        # over the whole buffer (so the GEMM and K1 agree on who owns what) and the bf16 GEMM engine
+        self._rs_mode = (bool(cfg.fuse_wgrad_rs) and self.p2p is not None and self.world > 1 and not self.fp32
+                         and not cfg.overlap and cfg.comm_algo != "oneshot")
+        self._rs_active = False                  # True only inside the fused step body
+        self._rs_dirty = True                    # owners' fc1 slices must be zero when a fused step starts
+        if self._rs_mode:
+            fc1w = spec.param("fc1_weight")
+            per = -(-(self.n // 4) // self.world) * 4
+            self._rs = N.GemmRS()
+            self._rs.world, self._rs.rank, self._rs.base, self._rs.per = self.world, self.p2p.rank, fc1w.offset, per
+            for r in range(self.world):
+                self._rs.out[r] = self._grad_ptrs[r]
         self.init_params(cfg.seed)
         self.opt_step = 0
         self._graph: Optional[torch.cuda.CUDAGraph] = None
@@ -380,8 +393,13 @@ class NativeEngine:
              workspace=ws, counters=cnt)
         # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket (K = batch: wide tiles
         # only pay off when K is long enough to amortise their epilogue)
-        gemm(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True,
-             bn=256 if (s.fc % 256 == 0 and B >= 512) else 128)
+        wbn = 256 if (s.fc % 256 == 0 and B >= 512) else 128
+        if self._rs_active:
+            # ... added tile by tile into the slice owners' buckets over NVLink: the reduce-scatter half of the
+            # gradient allreduce happens inside this GEMM, K1 only updates and broadcasts (prered range)
+            N.gemm_bf16_rs(flat, self.dh, s.flat_dim, s.fc, B, True, True, s.fc, wbn, self._rs)
+        else:
+            gemm(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=wbn)
 
     def _backward_conv(self, B: int):
         s = self.spec
@@ -516,6 +534,10 @@ class NativeEngine:
             self._masters_dirty = self._masters_dirty or a.n_sharded > 0
             self._slots_dirty = True                                   # slots of non-owned slices are not maintained
         a.grid = grid
+        if self._rs_active and peers and a.algo != 0:
+            fc1w = self.spec.param("fc1_weight")
+            a.n_prered = 1
+            a.prered_begin[0], a.prered_end[0] = fc1w.offset, fc1w.offset + fc1w.numel
         if advance:                                                     # iter_ += 1 in the same launch
             a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done.data_ptr()
             a.loss_src, a.loss_mail, a.loss_ring = self.loss_acc.data_ptr(), self._mail.data_ptr(), self._MAIL_RING
@@ -533,6 +555,7 @@ class NativeEngine:
         self._zero_step_accumulators()
         self._forward(self.B, True, True)
         self._backward(self.B)
+        self._rs_dirty = True
         return self._read_loss()
 
     def apply(self, lr: float) -> None:
@@ -581,8 +604,12 @@ class NativeEngine:
             self._zero_step_accumulators()
             self._forward(self.B, True, True)
         if not self.cfg.overlap:
-            self._backward(self.B)
-            self._update(peers=True)
+            self._rs_active = self._rs_mode
+            try:
+                self._backward(self.B)
+                self._update(peers=True)
+            finally:
+                self._rs_active = False
             return
         # Two buckets in gradient-ready order (SURVEY 5.5 "Overlap"): the fc bucket (98% of the
         # bytes) closes first and its fused allreduce+update runs on the comm stream underneath the
@@ -618,6 +645,12 @@ class NativeEngine:
         return self._await_loss(self.opt_step) if read_loss else 0.0
 
     def _run_step(self, mode: str):
+        if self._rs_mode and self._rs_dirty:
+            # an eager backward (compute_grads) stored a whole local gradient: put the owners' slices back to zero
+            self.G["fc1_weight"].zero_()
+            torch.cuda.synchronize()
+            self.p2p.barrier()
+            self._rs_dirty = False
         self._windowed = mode == "window"
         self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
         if self.cfg.cuda_graph:

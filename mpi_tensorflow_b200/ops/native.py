@@ -34,7 +34,13 @@ class FusedArgs(C.Structure):
         ("n_sharded", i32), ("shard_begin", i64 * 4), ("shard_end", i64 * 4),
         ("advance_step", vp), ("done_counter", vp),
         ("loss_src", vp), ("loss_mail", vp), ("loss_ring", i32),
+        ("n_prered", i32), ("prered_begin", i64 * 2), ("prered_end", i64 * 2),
     ]
+
+
+class GemmRS(C.Structure):
+    """mtb_gemm_rs: where the reduce-scatter epilogue of mtb_gemm_bf16_rs adds its tiles."""
+    _fields_ = [("world", i32), ("rank", i32), ("base", i64), ("per", i64), ("out", vp * 16)]
 
 
 _SIGS = {
@@ -47,6 +53,7 @@ _SIGS = {
     "mtb_enable_peer_access": [i32],
     "mtb_gemm_bf16": [vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, vp, i32, f32, u64, vp, i32, i32,
                       vp, vp, vp],
+    "mtb_gemm_bf16_rs": [vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, C.POINTER(GemmRS), vp],
     "mtb_gemm_tf32": [vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, vp, i32, f32, u64, vp, i32, i32, vp, vp, vp],
     "mtb_conv1_fwd_f32": [vp, vp, vp, vp, vp, i32, i32, vp],
     "mtb_conv1_wgrad_f32": [vp, vp, vp, vp, vp, vp, i32, i32, vp],
@@ -189,6 +196,14 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, M: int, N: in
     call("mtb_gemm_bf16", ptr(A), ptr(B), ptr(out), M, N, K, int(a_mn), int(b_mn), lda, ldb, ldc,
          int(out.dtype == torch.bfloat16), ptr(bias), int(relu), float(keep_prob), seed, ptr(step_ptr), bn, splits,
          ptr(workspace), ptr(counters))
+
+
+def gemm_bf16_rs(A: torch.Tensor, B: torch.Tensor, M: int, N: int, K: int, a_mn: bool, b_mn: bool, ldc: int, bn: int,
+                 rs: GemmRS) -> None:
+    """op(A) op(B) added into the owners' gradient slices over peer memory (GEMM -> reduce-scatter)."""
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
+    call("mtb_gemm_bf16_rs", ptr(A), ptr(B), M, N, K, int(a_mn), int(b_mn), A.stride(0), B.stride(0), ldc, bn,
+         C.byref(rs))
 
 
 def gemm_tf32(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, a_mn: bool, b_mn: bool,

@@ -63,12 +63,16 @@ def fused(comm, outdir):
     r, n, dev = comm.rank, comm.size, comm.device
     b, steps = 32, 6
     finals = {}
-    algos = ["oneshot", "twoshot"] + (["nvls"] if getattr(comm, "has_multicast", False) else [])
+    mc = getattr(comm, "has_multicast", False)
+    # "+rs": the FC1 weight gradient is reduce-scattered inside its GEMM (tiles added into the owner over NVLink)
+    algos = ["oneshot", "twoshot"] + (["nvls"] if mc else []) + ["twoshot+rs"] + (["nvls+rs"] if mc else [])
     print(f"rank {r}: allocator={'symm' if comm._symm is not None else 'ipc'} multicast={comm.has_multicast}", flush=True)
     for algo in algos:
         cfg = TrainConfig(model="tutorial512", batch=b, eval_every=0, log_every=0, dropout=False,
-                          comm_algo=algo, cuda_graph=(algo != "oneshot"), lr_decay_rows=10 ** 9)
+                          comm_algo=algo.split("+")[0], fuse_wgrad_rs=algo.endswith("+rs"),
+                          cuda_graph=(algo != "oneshot"), lr_decay_rows=10 ** 9)
         tr = Trainer(cfg, comm)
+        assert tr.engine._rs_mode == algo.endswith("+rs")
         # rank r trains on rows [r*b, (r+1)*b) of every global batch of n*b rows
         rows = steps * b + b
         u8, lab = D.synthetic_mnist(n * rows, 5)
