@@ -42,11 +42,13 @@ struct GemmParams {
   const long long* step_ptr;
   float* workspace;
   unsigned int* counters;
-  // Reduce-scatter epilogue (mtb_gemm_bf16_rs): instead of storing the tile, add it into the gradient buffer of the
-  // rank that owns each 16-byte vector (slice r = vectors [r*rs_per, (r+1)*rs_per) of the flat buffer), over NVLink.
-  int rs_world;
+#ifdef MTB_GEMM_RS_TU
+  // Reduce-scatter epilogue (gemm_rs_sm100.cu compiles this file a second time with MTB_GEMM_RS_TU): instead of storing
+  // the tile, add it into the gradient buffer of the rank that owns each 16-byte vector (slice r = vectors
+  // [r*rs_per/4, (r+1)*rs_per/4) of the flat buffer), over NVLink.
   long long rs_base, rs_per;           // flat element offset of out[0][0]; elements per owner slice (multiple of 4)
   float* rs_out[16];                   // every rank's flat gradient buffer (peer-mapped)
+#endif
   int stages;                          // smem ring depth actually used (<= Cfg::kStages): short-K problems take
                                        // fewer so that several CTAs fit on one SM and their epilogues overlap
 };
@@ -99,7 +101,8 @@ __device__ __forceinline__ void epilogue_store(const GemmParams& p, const float 
     } else {
       for (int j = 0; j < 32 && gcol0 + j < p.N; ++j) dst[j] = __float2bfloat16(o[j]);
     }
-  } else if (p.rs_world > 1) {
+#ifdef MTB_GEMM_RS_TU
+  } else if (true) {
     // GEMM -> reduce-scatter in one kernel: every rank adds its tile into the owner's slice while the other CTAs
     // are still multiplying.  red.v4.f32 at system scope: the sum is read only after the consumer's flag barrier.
     const long long flat0 = p.rs_base + (long long)grow * p.ldc + gcol0;
@@ -119,6 +122,7 @@ __device__ __forceinline__ void epilogue_store(const GemmParams& p, const float 
         asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(dst), "f"(o[j]) : "memory");
       }
     }
+#endif
   } else {
     float* dst = reinterpret_cast<float*>(p.out) + (long long)grow * p.ldc + gcol0;
     if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
@@ -389,6 +393,50 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
 
 }  // namespace
 
+#ifdef MTB_GEMM_RS_TU
+
+extern "C" {
+
+// D = op(A) op(B) ADDED into the gradient buffers of the ranks that own each slice (GEMM -> reduce-scatter in one
+// kernel over NVLink peer memory).  Element (i, j) of the product lands at flat index rs->base + i*ldc + j of rank
+// ((flat / 4) / (rs->per / 4))'s buffer rs->out[rank].  Owners' slices must be zero (or hold earlier partial sums) and
+// nobody may read them until every rank's call has completed and a cross-GPU barrier has passed: that is what
+// mtb_fused_allreduce_update does for ranges declared in mtb_fused_args.prered_*.  Instantiated for the
+// weight-gradient form only (X^T * dY: both operands MN-major, bn 128 or 256).
+int mtb_gemm_bf16_rs(const void* A, const void* B, int M, int N, int K, int a_mn_major, int b_mn_major, long long lda,
+                     long long ldb, long long ldc, int bn, const mtb_gemm_rs* rs, cudaStream_t stream) {
+  MTB_REQUIRE(A && B && rs && M > 0 && N > 0 && K > 0, "gemm_rs: null pointer or empty shape");
+  MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm_rs: operand row pitch must be a multiple of 16 bytes");
+  MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_rs: operands must be 16-byte aligned");
+  MTB_REQUIRE(a_mn_major && b_mn_major && (bn == 128 || bn == 256), "gemm_rs: MN-major x MN-major, bn 128 or 256");
+  MTB_REQUIRE(rs->world > 1 && rs->world <= 16 && rs->rank >= 0 && rs->rank < rs->world, "gemm_rs: bad world / rank");
+  MTB_REQUIRE(rs->base % 4 == 0 && rs->per > 0 && rs->per % 4 == 0 && ldc % 4 == 0,
+              "gemm_rs: base, slice size and ldc must be multiples of 4 elements");
+  MTB_REQUIRE((rs->base + (long long)(M - 1) * ldc + N - 1) / rs->per < rs->world, "gemm_rs: output exceeds the slices");
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_total = (int)mtb::ceil_div(K, BK);
+  p.kb_per_split = p.kb_total;
+  p.splits = 1;
+  p.out = rs->out[rs->rank]; p.ldc = ldc; p.out_bf16 = 0; p.bias = nullptr; p.relu = 0;
+  p.keep_prob = 1.0f; p.seed = 0; p.step_ptr = nullptr;
+  p.workspace = nullptr; p.counters = nullptr;
+  p.rs_base = rs->base; p.rs_per = rs->per;
+  for (int r = 0; r < 16; ++r) p.rs_out[r] = nullptr;
+  for (int r = 0; r < rs->world; ++r) {
+    MTB_REQUIRE(rs->out[r] != nullptr, "gemm_rs: null peer buffer");
+    p.rs_out[r] = reinterpret_cast<float*>(rs->out[r]);
+  }
+  CUtensorMap ma, mb;
+  MTB_REQUIRE(get_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, 64, 64), "gemm_rs: tensor map for A failed");
+  MTB_REQUIRE(get_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64, 64), "gemm_rs: tensor map for B failed");
+  return bn == 128 ? launch<128, true, true>(ma, mb, p, stream) : launch<256, true, true>(ma, mb, p, stream);
+}
+
+}  // extern "C"
+
+#else  // the regular library entry points
+
 extern "C" {
 
 size_t mtb_gemm_workspace_bytes(int M, int N, int bn, int splits) {
@@ -403,14 +451,10 @@ size_t mtb_gemm_counter_bytes(int M, int N, int bn) {
   return (size_t)mtb::ceil_div(M, BM) * (size_t)mtb::ceil_div(N, bn) * sizeof(unsigned int);
 }
 
-}  // extern "C"
-
-namespace {
-
-int gemm_bf16_impl(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major, int b_mn_major,
-                   long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
-                   float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
-                   void* workspace, void* counters, const mtb_gemm_rs* rs, cudaStream_t stream) {
+int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major, int b_mn_major,
+                  long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
+                  float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
+                  void* workspace, void* counters, cudaStream_t stream) {
   MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm: null pointer or empty shape");
   MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm: operand row pitch must be a multiple of 16 bytes");
   MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: operands must be 16-byte aligned");
@@ -428,21 +472,6 @@ int gemm_bf16_impl(const void* A, const void* B, void* out, int M, int N, int K,
   p.keep_prob = keep_prob; p.seed = seed; p.step_ptr = step_ptr;
   p.workspace = reinterpret_cast<float*>(workspace);
   p.counters = reinterpret_cast<unsigned int*>(counters);
-  p.rs_world = 0; p.rs_base = 0; p.rs_per = 4;
-  for (int r = 0; r < 16; ++r) p.rs_out[r] = nullptr;
-  if (rs != nullptr) {
-    MTB_REQUIRE(rs->world > 1 && rs->world <= 16 && rs->rank >= 0 && rs->rank < rs->world, "gemm_rs: bad world / rank");
-    MTB_REQUIRE(!out_bf16 && splits == 1 && bias == nullptr && !relu && keep_prob >= 1.0f,
-                "gemm_rs: fp32 output, no split-K, no bias / ReLU / dropout");
-    MTB_REQUIRE(rs->base % 4 == 0 && rs->per > 0 && rs->per % 4 == 0 && ldc % 4 == 0,
-                "gemm_rs: base, slice size and ldc must be multiples of 4 elements");
-    MTB_REQUIRE((rs->base + (long long)(M - 1) * ldc + N - 1) / rs->per < rs->world, "gemm_rs: output exceeds the slices");
-    p.rs_world = rs->world; p.rs_base = rs->base; p.rs_per = rs->per;
-    for (int r = 0; r < rs->world; ++r) {
-      MTB_REQUIRE(rs->out[r] != nullptr, "gemm_rs: null peer buffer");
-      p.rs_out[r] = reinterpret_cast<float*>(rs->out[r]);
-    }
-  }
   // Cluster shape: share the operand whose tile dimension the grid divides evenly.  Instantiated for
   // the three products of the FC layers: fprop (BN 64, A K-major, B MN-major) and wgrad (BN 128,
   // both MN-major) share A across 4 or 2 CTAs along N; dgrad (BN 128, both K-major) shares B along M.
@@ -483,30 +512,6 @@ int gemm_bf16_impl(const void* A, const void* B, void* out, int M, int N, int K,
   MTB_GEMM_CASE(256, true, true)
 #undef MTB_GEMM_CASE
   return mtb_set_error_msg(MTB_E_ARG, "gemm: no kernel variant", __FILE__, __LINE__);
-}
-
-}  // namespace
-
-extern "C" {
-
-int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major, int b_mn_major,
-                  long long lda, long long ldb, long long ldc, int out_bf16, const float* bias, int relu,
-                  float keep_prob, unsigned long long seed, const long long* step_ptr, int bn, int splits,
-                  void* workspace, void* counters, cudaStream_t stream) {
-  return gemm_bf16_impl(A, B, out, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, out_bf16, bias, relu, keep_prob, seed,
-                        step_ptr, bn, splits, workspace, counters, nullptr, stream);
-}
-
-// D = op(A) op(B) ADDED into the gradient buffers of the ranks that own each slice (GEMM -> reduce-scatter in one
-// kernel over NVLink peer memory).  Element (i, j) of the product lands at flat index rs->base + i*ldc + j of rank
-// ((flat / 4) / (rs->per / 4))'s buffer rs->out[rank].  Owners' slices must be zero (or hold earlier partial sums) and
-// nobody may read them until every rank's call has completed and a cross-GPU barrier has passed: that is what
-// mtb_fused_allreduce_update does for ranges declared in mtb_fused_args.prered_*.
-int mtb_gemm_bf16_rs(const void* A, const void* B, int M, int N, int K, int a_mn_major, int b_mn_major, long long lda,
-                     long long ldb, long long ldc, int bn, const mtb_gemm_rs* rs, cudaStream_t stream) {
-  MTB_REQUIRE(rs != nullptr, "gemm_rs: null descriptor");
-  return gemm_bf16_impl(A, B, rs->out[rs->rank >= 0 && rs->rank < 16 ? rs->rank : 0], M, N, K, a_mn_major, b_mn_major,
-                        lda, ldb, ldc, 0, nullptr, 0, 1.0f, 0ull, nullptr, bn, 1, nullptr, nullptr, rs, stream);
 }
 
 // fp32 operands, TF32 tensor-core math, fp32 accumulation and output (the "fp32" configs of BASELINE.json; the
@@ -664,3 +669,5 @@ int mtb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* out, int M,
 }
 
 }  // extern "C"
+
+#endif  // MTB_GEMM_RS_TU

@@ -13,6 +13,7 @@ Run ``python -m mpi_tensorflow_b200.ops.build`` (add ``--force`` to rebuild).
 from __future__ import annotations
 
 import hashlib
+import re
 import shlex
 import os
 import shutil
@@ -97,7 +98,9 @@ def build_cuda(force: bool = False, verbose: bool = False, jobs: int = 8) -> Pat
     def compile_one(src: Path) -> Path:
         obj = OBJDIR / (src.stem + ".o")
         stamp = OBJDIR / (src.stem + ".stamp")
-        d = _digest([src], hdr_digest)
+        # a .cu that includes another .cu (gemm_rs_sm100.cu) depends on it too
+        deps = [CSRC / m for m in re.findall(r'#include "(\w+\.cu)"', src.read_text())]
+        d = _digest([src] + deps, hdr_digest)
         if not force and _stamp_ok(stamp, d, obj):
             return obj
         out = _run([NVCC, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)], log=OBJDIR / (src.stem + ".log"))
