@@ -48,6 +48,7 @@ struct GemmParams {
   // [r*rs_per/4, (r+1)*rs_per/4) of the flat buffer), over NVLink.
   long long rs_base, rs_per;           // flat element offset of out[0][0]; elements per owner slice (multiple of 4)
   float* rs_out[16];                   // every rank's flat gradient buffer (peer-mapped)
+  int rs_staged;                       // 1: transpose each 32x32 chunk through smem so a warp adds whole 128-byte row segments
 #endif
   int stages;                          // smem ring depth actually used (<= Cfg::kStages): short-K problems take
                                        // fewer so that several CTAs fit on one SM and their epilogues overlap
@@ -134,6 +135,34 @@ __device__ __forceinline__ void epilogue_store(const GemmParams& p, const float 
     }
   }
 }
+
+#ifdef MTB_GEMM_RS_TU
+// The TMEM read gives each lane one ROW of a 32x32 chunk, so adding it as is sends 32 separate 16-byte atomics per
+// instruction across NVLink.  Transposed through a padded shared-memory tile, 8 lanes cover 128 contiguous bytes of
+// one row and an instruction touches 4 row segments: the remote additions coalesce.  `stg` is this warp's 32x33 tile
+// in the (by now idle) operand ring.
+__device__ __forceinline__ void rs_store_staged(const GemmParams& p, const float (&v)[32], float* stg, int grow0, int lane,
+                                                int gcol0) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = v[j];
+  __syncwarp();
+  const int sub = lane >> 3, c4 = (lane & 7) * 4;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int r = 4 * k + sub;
+    const int grow = grow0 + r;
+    if (grow < p.M) {
+      const float* src = stg + r * 33 + c4;
+      const long long flat = p.rs_base + (long long)grow * p.ldc + gcol0 + c4;
+      float* dst = p.rs_out[(flat >> 2) / (p.rs_per >> 2)] + flat;
+      asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(src[0]), "f"(src[1]),
+                   "f"(src[2]), "f"(src[3])
+                   : "memory");
+    }
+  }
+  __syncwarp();
+}
+#endif
 
 // CM x CN thread-block clusters: the CN CTAs of a cluster row work on the same M tile and each
 // loads 1/CN of the A tile, multicast to all of them; the CM CTAs of a cluster column share the
@@ -292,6 +321,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+#ifdef MTB_GEMM_RS_TU
+        if (p.rs_staged && tile_n * BN + c * 32 + 32 <= p.N) {
+          rs_store_staged(p, v, reinterpret_cast<float*>(sA) + q * (32 * 33), tile_m * BM + q * 32, lane,
+                          tile_n * BN + c * 32);
+          continue;
+        }
+#endif
         epilogue_store(p, v, grow, tile_n * BN + c * 32, step);
       }
     } else {
@@ -422,6 +458,7 @@ int mtb_gemm_bf16_rs(const void* A, const void* B, int M, int N, int K, int a_mn
   p.keep_prob = 1.0f; p.seed = 0; p.step_ptr = nullptr;
   p.workspace = nullptr; p.counters = nullptr;
   p.rs_base = rs->base; p.rs_per = rs->per;
+  p.rs_staged = (rs->flags & 1) ? 0 : 1;
   for (int r = 0; r < 16; ++r) p.rs_out[r] = nullptr;
   for (int r = 0; r < rs->world; ++r) {
     MTB_REQUIRE(rs->out[r] != nullptr, "gemm_rs: null peer buffer");

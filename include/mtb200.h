@@ -55,6 +55,8 @@ typedef struct {
   long long base;       /* flat element offset of the product's element (0,0) */
   long long per;        /* elements per owner slice, multiple of 4 (same partition as the two-shot / nvls update) */
   void* out[16];        /* every rank's flat fp32 gradient buffer, peer-mapped */
+  int flags;            /* bit 0: add straight from the TMEM row layout (one 16-byte atomic per lane) instead of staging
+                         * each chunk through shared memory so that a warp adds whole 128-byte row segments */
 } mtb_gemm_rs;
 int mtb_gemm_bf16_rs(const void* A, const void* B, int M, int N, int K, int a_mn_major, int b_mn_major, long long lda,
                      long long ldb, long long ldc, int bn, const mtb_gemm_rs* rs, cudaStream_t stream);

@@ -71,6 +71,7 @@ class NativeEngine:
             per = -(-(self.n // 4) // self.world) * 4
             self._rs = N.GemmRS()
             self._rs.world, self._rs.rank, self._rs.base, self._rs.per = self.world, self.p2p.rank, fc1w.offset, per
+            self._rs.flags = 1 if os.environ.get("MTB_RS_STAGED", "1") == "0" else 0
             for r in range(self.world):
                 self._rs.out[r] = self._grad_ptrs[r]
         self.init_params(cfg.seed)

@@ -40,7 +40,7 @@ class FusedArgs(C.Structure):
 
 class GemmRS(C.Structure):
     """mtb_gemm_rs: where the reduce-scatter epilogue of mtb_gemm_bf16_rs adds its tiles."""
-    _fields_ = [("world", i32), ("rank", i32), ("base", i64), ("per", i64), ("out", vp * 16)]
+    _fields_ = [("world", i32), ("rank", i32), ("base", i64), ("per", i64), ("out", vp * 16), ("flags", i32)]
 
 
 _SIGS = {

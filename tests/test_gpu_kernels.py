@@ -446,3 +446,32 @@ def test_conv2_backward_with_fused_unpool(N, dev, B):
     assert _rel(dW, dW_ref) < 1e-5 and _rel(db, db_ref) < 1e-5
     ref = O.conv5x5_dgrad(dA.cpu().float(), w.cpu().float(), (B, 14, 14, 32))
     assert _rel(dx.cpu(), ref) < 5e-3
+
+
+# ----------------------------------------------------------------------------- GEMM -> reduce-scatter epilogue
+@pytest.mark.parametrize("staged", [True, False])
+@pytest.mark.parametrize("bn,world,K", [(128, 3, 100), (256, 2, 64), (128, 8, 1024)])
+def test_gemm_reduce_scatter_epilogue(N, dev, bn, world, K, staged):
+    """mtb_gemm_bf16_rs adds X^T dY into whichever "rank's" buffer owns each 16-byte vector.  The kernel does not
+    care whether a buffer is peer or local memory, so one GPU with `world` local buffers checks the routing."""
+    M, Nn, base = 3136, 512, 1024                      # fc1 wgrad of the tutorial model, ragged last M tile
+    X = _bf(torch.randn(K, M)).to(dev)                 # MN-major A: stored [K, M]
+    dY = _bf(torch.randn(K, Nn)).to(dev)               # MN-major B: stored [K, N]
+    total = base + M * Nn + 512
+    per = -(-(total // 4) // world) * 4
+    bufs = [torch.ones(total, device=dev) for _ in range(world)]
+    rs = N.GemmRS()
+    rs.world, rs.rank, rs.base, rs.per, rs.flags = world, 1, base, per, 0 if staged else 1
+    for r in range(world):
+        rs.out[r] = bufs[r].data_ptr()
+    for _ in range(2):                                 # it ADDS: two calls leave twice the product
+        N.gemm_bf16_rs(X, dY, M, Nn, K, True, True, Nn, bn, rs)
+    torch.cuda.synchronize()
+    prod = (X.float().t() @ dY.float()).reshape(-1)
+    owner = (torch.arange(base, base + M * Nn, device=dev) // 4) // (per // 4)
+    for r in range(world):
+        got = bufs[r][base:base + M * Nn] - 1.0
+        want = torch.where(owner == r, 2.0 * prod, torch.zeros_like(prod))
+        assert _rel(got, want) < 1e-5 + 2e-5 * K / 2048, (r, _rel(got, want))
+        assert torch.equal(got[owner != r], torch.zeros_like(got[owner != r]))
+        assert float(bufs[r][:base].min()) == 1.0 and float(bufs[r][base + M * Nn:].max()) == 1.0
