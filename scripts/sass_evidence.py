@@ -4,7 +4,7 @@ so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "
 out = subprocess.run(["cuobjdump", "-sass", so], stdout=subprocess.PIPE, text=True).stdout
 pat = {"UTC*MMA (tcgen05.mma)": r"\bUTC\w*MMA\b", "LDTM (tcgen05.ld)": r"\bLDTM\b", "UTMALDG (TMA load)": r"\bUTMALDG\b",
        "UTCBAR (tcgen05.commit)": r"\bUTCBAR\b", "SYNCS (mbarrier)": r"\bSYNCS\b", "multimem": r"\bLDGMC\b|\bSTGMC\b|\bREDGMC\b|MULTIMEM",
-       "LD.E.*.SYS (peer loads)": r"\bLD\.E\S*\.SYS\b|LDG\.E\S*\.SYS", "HMMA (legacy mma.sync)": r"\bHMMA\b"}
+       "LD.E.*.SYS (peer loads)": r"\bLD\.E\S*\.SYS\b|LDG\.E\S*\.SYS", "REDG..SYS (peer atomics)": r"\bREDG\.E\S*\.SYS\b", "HMMA (legacy mma.sync)": r"\bHMMA\b"}
 fn = None
 counts = collections.OrderedDict()
 for line in out.splitlines():

@@ -5,7 +5,7 @@ so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "
 out = subprocess.run(["cuobjdump", "-sass", so], stdout=subprocess.PIPE, text=True).stdout
 keep = re.compile(r"\b(UTC\w*MMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UTMAPF|UTMACCTL|SYNCS|LDGMC|STGMC|REDGMC|ELECT|"
                   r"ACQBULK|PREEXIT|ACQSHMINIT|FENCE\.VIEW\.ASYNC\S*|LD\.E\S*\.SYS\S*|LDG\.E\S*\.SYS\S*|ST\.E\S*\.SYS\S*|"
-                  r"STG\.E\S*\.SYS\S*|UCGABAR_ARV|UCGABAR_WAIT|HMMA)\b")
+                  r"STG\.E\S*\.SYS\S*|REDG\.E\S*\.SYS|UCGABAR_ARV|UCGABAR_WAIT|HMMA)\b")
 fn, lines, total = None, [], 0
 def flush():
     global lines
