@@ -13,7 +13,6 @@ None of this package's kernels, engine or communicator is used here.
 """
 from __future__ import annotations
 
-import json
 import os
 
 import torch

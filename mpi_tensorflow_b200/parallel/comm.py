@@ -19,7 +19,7 @@ from __future__ import annotations
 
 import os
 import threading
-from typing import List, Optional, Sequence
+from typing import List, Optional
 
 import numpy as np
 import torch

@@ -18,7 +18,7 @@ import gzip
 import os
 import struct
 from dataclasses import dataclass
-from typing import Optional, Tuple
+from typing import Tuple
 
 import numpy as np
 

@@ -1,5 +1,5 @@
 """Count the Blackwell-native SASS mnemonics per kernel in libmtb200.so (cuobjdump -sass)."""
-import collections, re, subprocess, sys, os
+import collections, re, subprocess, os
 so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mpi_tensorflow_b200", "lib", "libmtb200.so")
 out = subprocess.run(["cuobjdump", "-sass", so], stdout=subprocess.PIPE, text=True).stdout
 pat = {"UTC*MMA (tcgen05.mma)": r"\bUTC\w*MMA\b", "LDTM (tcgen05.ld)": r"\bLDTM\b", "UTMALDG (TMA load)": r"\bUTMALDG\b",

@@ -1,6 +1,6 @@
 """Per-kernel SASS excerpt of libmtb200.so: every tensor-core / TMA / TMEM / mbarrier / multimem / peer-memory
 instruction with its address (cuobjdump -sass, encodings stripped).  Complements sass_evidence.py (counts only)."""
-import os, re, subprocess, sys
+import os, re, subprocess
 so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mpi_tensorflow_b200", "lib", "libmtb200.so")
 out = subprocess.run(["cuobjdump", "-sass", so], stdout=subprocess.PIPE, text=True).stdout
 keep = re.compile(r"\b(UTC\w*MMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UTMAPF|UTMACCTL|SYNCS|LDGMC|STGMC|REDGMC|ELECT|"
