@@ -264,3 +264,33 @@ def test_loss_mailbox_decoding_without_a_gpu():
         NativeEngine._await_loss(eng, 6, timeout=0.05)         # never mailed
     post(2 ** 31 + 7, 0.5)                                     # step numbers with the top bit set decode too
     assert NativeEngine._await_loss(eng, 2 ** 31 + 7) == 0.5
+
+
+def test_crash_then_resume_matches_uninterrupted_run(tmp_path):
+    """Failure detection + checkpoint/resume through the command line: a rank dies at step 9,
+    the launcher takes the job down, a second launch resumes from the last checkpoint and ends with exactly
+    the parameters, momentum and step counter of a run that never crashed."""
+    root = os.path.dirname(os.path.dirname(__file__))
+    env = dict(os.environ, PYTHONPATH=root)
+    env.pop("MTB_FAULT", None)
+
+    def launch(ckdir, extra=(), fault=None):
+        cmd = [sys.executable, "-m", "mpi_tensorflow_b200.parallel.launch", "-np", "2", "--timeout", "240", "-m",
+               "mpi_tensorflow_b200", "--device", "cpu", "--backend", "shm", "--model", "tiny", "--batch", "16",
+               "--max-steps", "12", "--eval-every", "0", "--log-every", "0", "--step-timeout-s", "20",
+               "--checkpoint-dir", str(ckdir), "--checkpoint-every", "4", *extra]
+        e = dict(env, MTB_FAULT=fault) if fault else env
+        return subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=e, timeout=300)
+
+    a, b = tmp_path / "a", tmp_path / "b"
+    p = launch(a)
+    assert p.returncode == 0, p.stdout[-2000:]
+    p = launch(b, fault="rank=1,step=9,kind=exit")
+    assert p.returncode != 0, "the job must fail when a rank dies"
+    assert (b / "model.ckpt-8.index").exists() and not (b / "model.ckpt-12.index").exists(), p.stdout[-2000:]
+    p = launch(b, extra=("--resume", str(b / "model.ckpt-8")))
+    assert p.returncode == 0, p.stdout[-2000:]
+    want, got = ckpt.load(str(a / "model.ckpt-12")), ckpt.load(str(b / "model.ckpt-12"))
+    assert set(want) == set(got) and len(want) >= 9
+    for k in want:
+        assert np.array_equal(want[k], got[k]), k
