@@ -11,8 +11,9 @@ its autodiff (``minimize``, ``mpipy.py:65``) and its allocator (``mpipy.py:69-71
 * the step captured in a CUDA graph: one launch per step, no per-step H2D, the
   step counter / LR schedule / dropout stream all live on the device.
 
-Precision: bf16 activations and bf16 tensor-core operands, fp32 accumulation,
-fp32 master weights, optimizer state and gradients.
+Precision: ``dtype="bf16"`` - bf16 activations and bf16 tensor-core operands, fp32 accumulation,
+fp32 master weights, optimizer state and gradients; ``dtype="fp32"`` - fp32 everywhere, the
+GEMM-shaped products as TF32 tensor-core MMAs (the generic kernel set, ``*_f32`` entry points).
 """
 from __future__ import annotations
 
@@ -667,9 +668,10 @@ class NativeEngine:
         (``hx`` [rows, 784] fp32, ``hy`` [rows] int32), walked with the reference's sequential
         window (``mpipy.py:80-82``).  This is the reference's feed loop (``mpipy.py:83-85``: one
         host->device feed per step) done the B200 way: step i+1's batch is copied on a copy
-        stream into the other half of a double buffer while step i computes, and each step's
-        loss is copied back to a pinned ring that the host reads a few steps later, so neither
-        transfer ever stalls the GPU.  Returns the loss of every step."""
+        stream into the other half of a double buffer while step i computes (one CUDA graph per
+        half, so the kernels read it in place), and each step's loss is mailed by the update
+        kernel into a pinned host ring (:meth:`_await_loss`) that the host polls a few steps
+        later, so neither transfer ever stalls the GPU.  Returns the loss of every step."""
         B, dev = self.B, self.device
         if not (hx.is_pinned() and hy.is_pinned()):
             raise ValueError("stream_steps needs pinned host tensors (tensor.pin_memory())")
