@@ -18,7 +18,22 @@
 //             2*(N-1)/N*S bytes per GPU.  Optimizer slots sharded (ZeRO-1 style).
 //   nvls      as two-shot, but multimem.ld_reduce pulls the switch-reduced slice in one load
 //             and multimem.st broadcasts the result (needs a multicast mapping).
+//   push      one-shot for the small bucket that closes a step: every rank STORES its gradients
+//             into a receive row on each peer (double buffered by step parity), signals once,
+//             and reduces its local rows.  One flag round instead of two: the closing round is
+//             replaced by the parity (a row is rewritten two steps later, and a rank can only
+//             get there after every peer has signalled the step in between).
 // Every rank sums in the same order, so replicas stay bit-identical.
+//
+// The same kernel averages PARAMETERS in place (the reference's own strategy, mpipy.py:95-153):
+// grads := params, optimizer = none, two-shot / nvls (an owner is the only reader of its slice
+// on every peer, so in-place is race free), dst_mask = which ranks receive the mean
+// (bit 0 only = the reference's root-only assign, mpipy.py:129).
+//
+// It also returns the step's loss the way the reference defines it (mpipy.py:55-58): each launch
+// sums 0.5*w^2 over the weight-decay ranges it walks (block partials in block order, so the value is
+// reproducible), slice owners exchange their partial through tagged 8-byte slots, and the launch that
+// advances the step mails CE + wd*L2 and the batch's error count to the host.
 //
 // Flag protocol: one 32-bit slot per (block, peer) in each rank's signal pad, written with
 // st.release.sys after a system fence and polled with ld.acquire.sys.  Values are a per-block
@@ -34,6 +49,8 @@ using namespace mtb;
 constexpr int kMaxRanks = 16;
 constexpr int kMaxBlocks = 512;
 constexpr int kMaxRanges = 8;
+constexpr int kChanBlocks = kMaxBlocks / 2;         // two channels of flag / sequence blocks (concurrent launches)
+constexpr int kL2Rows = 4;                          // launches of one step that can contribute an L2 partial
 constexpr long long kSpinLimit = 30000000000ll;     // ~15 s at 2 GHz
 
 struct FusedParams {
@@ -70,6 +87,19 @@ struct FusedParams {
   const float* loss_src;                            // step result mailed to the host by the last block (may be null)
   unsigned long long* loss_mail;                    // pinned host ring of {f32 loss, u32 step} words
   int loss_ring;
+  int chan_base;                                    // first flag / sequence block of this launch's channel
+  float* push_recv[kMaxRanks];                      // push: every rank's receive area [2 parity][world][push_stride]
+  long long push_stride;
+  const __nv_bfloat16* grads_lp[kMaxRanks];         // bf16 wire format: gradients of [lp_begin, lp_end) live here
+  const __nv_bfloat16* mc_grads_lp;
+  long long lp_begin, lp_end;
+  unsigned dst_mask;                                // two-shot: ranks that receive the result (0 = all)
+  float* l2_blocks;                                 // per-block partials of 0.5*sum(w^2) (null: no L2 value wanted)
+  unsigned long long* l2_slots[kMaxRanks];          // every rank's [kL2Rows][kMaxRanks] tagged {step+1 : f32} words
+  int l2_row;
+  int l2_rows_n[kL2Rows];                           // mailing launch: entries to add per row (0 unused, 1 local, world sliced)
+  const int* err_src;                               // batch error count, mailed next to the loss
+  unsigned long long* aux_mail;                     // pinned host ring of {u32 errors, u32 step} words
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -87,6 +117,26 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
                : "l"(p)
                : "memory");
   return v;
+}
+__device__ __forceinline__ float4 ld_peer_bf16x4(const __nv_bfloat16* p) {
+  uint32_t a, b;
+  asm volatile("ld.relaxed.sys.global.v2.b32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+  const float2 lo = unpack_bf16x2(a), hi = unpack_bf16x2(b);
+  return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+// switch-reduced bf16 gradients: the switch accumulates in fp32 and rounds the sum once
+__device__ __forceinline__ float4 multimem_ld_reduce_bf16x4(const __nv_bfloat16* p) {
+  uint32_t a, b;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0,%1}, [%2];"
+               : "=r"(a), "=r"(b)
+               : "l"(p)
+               : "memory");
+  const float2 lo = unpack_bf16x2(a), hi = unpack_bf16x2(b);
+  return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
 }
 __device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* p) {
   float4 v;
@@ -108,7 +158,8 @@ __device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* p, uint2 v) {
 // All ranks' block `b` meet here.  With `fence`, every thread first makes its own stores (to
 // peer memory) visible system-wide; without, the barrier only orders control flow, which is
 // all the opening round needs: the gradients it guards were written by earlier kernels, and a
-// kernel boundary already made them visible to peer loads.
+// kernel boundary already made them visible to peer loads.  `b` is the absolute flag block
+// (channel base + block index).
 __device__ void cross_gpu_barrier(const FusedParams& p, int b, uint32_t val, bool fence) {
   if (fence) __threadfence_system();
   __syncthreads();
@@ -131,9 +182,8 @@ struct Hyper {
   float lr, bc_lr;      // bc_lr: Adam's bias-corrected step size
 };
 
-__device__ __forceinline__ Hyper make_hyper(const FusedParams& p) {
+__device__ __forceinline__ Hyper make_hyper(const FusedParams& p, long long step) {
   Hyper h;
-  const long long step = p.step_ptr ? *p.step_ptr : 0;
   float lr = p.lr0;
   if (p.lr_override >= 0.f) {
     lr = p.lr_override;
@@ -172,11 +222,17 @@ __device__ __forceinline__ bool prereduced(const FusedParams& p, long long i) {
   return s;
 }
 
-// One float4 of the optimizer.  g is the already averaged gradient.
-__device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g) {
-  float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
+__device__ __forceinline__ bool low_precision(const FusedParams& p, long long i) {
+  return i >= p.lp_begin && i < p.lp_end;
+}
+
+// One float4 of the optimizer.  g is the already averaged gradient.  l2 collects 0.5*w^2 of the
+// weights BEFORE the update over the weight-decay ranges (the L2 term of the loss, mpipy.py:57-58).
+__device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g, float& l2) {
   if (p.optimizer < 0) return g;
-  if (p.wd != 0.f && decays(p, i)) {            // L2 term: grad += wd * w (mpipy.py:57-58)
+  float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
+  if (p.n_ranges > 0 && decays(p, i)) {         // L2 term: grad += wd * w (mpipy.py:57-58)
+    l2 += 0.5f * (w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w);
     g.x = fmaf(p.wd, w.x, g.x); g.y = fmaf(p.wd, w.y, g.y); g.z = fmaf(p.wd, w.z, g.z); g.w = fmaf(p.wd, w.w, g.w);
   }
   if (p.optimizer == 0) {
@@ -206,15 +262,18 @@ __device__ __forceinline__ uint2 to_bf16x4(float4 w) {
   return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
 }
 
-enum Kind { kLocal = 0, kOneShot = 1, kTwoShot = 2, kNvls = 3 };
+enum Kind { kLocal = 0, kOneShot = 1, kTwoShot = 2, kNvls = 3, kPush = 4 };
 
 // Vectors [lo, hi) of the bucket, kUnroll per thread per pass: all reductions (peer loads or
 // switch-reduced multimem loads) of a pass are issued before any of them is used, which is what
-// keeps enough bytes in flight to cover NVLink latency.
+// keeps enough bytes in flight to cover NVLink latency.  `recv` (push only): this rank's receive
+// rows of the current parity, [world][push_stride].
 template <int KIND>
-__device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, long long lo, long long hi) {
+__device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, long long lo, long long hi, float& l2,
+                                          const float* recv = nullptr) {
   constexpr int kUnroll = 4;
   const long long stride = (long long)gridDim.x * blockDim.x;
+  const bool has_lp = p.lp_end > p.lp_begin;
   for (long long v0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * kUnroll) {
     float4 g[kUnroll];
 #pragma unroll
@@ -224,10 +283,26 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
       if (v < hi) {
         const long long i = p.offset + (v << 2);
         if (KIND == kLocal) {
-          g[u] = *reinterpret_cast<const float4*>(p.grads[0] + i);
+          g[u] = (has_lp && low_precision(p, i)) ? ld_peer_bf16x4(p.grads_lp[0] + i)
+                                                 : *reinterpret_cast<const float4*>(p.grads[0] + i);
+        } else if (KIND == kPush) {
+          for (int r = 0; r < p.world; ++r) {       // rank order; my own row is the gradient buffer itself
+            const float4 t = r == p.rank ? *reinterpret_cast<const float4*>(p.grads[r] + i)
+                                         : ld_peer_f4(recv + r * p.push_stride + (v << 2));
+            g[u].x += t.x; g[u].y += t.y; g[u].z += t.z; g[u].w += t.w;
+          }
         } else if ((KIND == kNvls || KIND == kTwoShot) && p.n_prered > 0 && prereduced(p, i)) {
           g[u] = ld_peer_f4(p.grads[p.rank] + i);            // summed in place by the producers' epilogues
           *reinterpret_cast<float4*>(const_cast<float*>(p.grads[p.rank]) + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (has_lp && low_precision(p, i)) {          // bf16 on the wire, fp32 from here on
+          if (KIND == kNvls) {
+            g[u] = multimem_ld_reduce_bf16x4(p.mc_grads_lp + i);
+          } else {
+            for (int r = 0; r < p.world; ++r) {
+              const float4 t = ld_peer_bf16x4(p.grads_lp[r] + i);
+              g[u].x += t.x; g[u].y += t.y; g[u].z += t.z; g[u].w += t.w;
+            }
+          }
         } else if (KIND == kNvls) {
           g[u] = multimem_ld_reduce_f4(p.mc_grads + i);
         } else {
@@ -245,9 +320,9 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
       const long long i = p.offset + (v << 2);
       float4 gs = g[u];
       gs.x *= p.scale; gs.y *= p.scale; gs.z *= p.scale; gs.w *= p.scale;
-      const float4 w = apply_update(p, h, i, gs);
+      const float4 w = apply_update(p, h, i, gs, l2);
       const uint2 wb = to_bf16x4(w);
-      if (KIND == kLocal || KIND == kOneShot) {
+      if (KIND == kLocal || KIND == kOneShot || KIND == kPush) {
         *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
         if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = wb;
       } else if (KIND == kNvls) {
@@ -258,6 +333,7 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
       } else {
         const bool sharded = master_sharded(p, i);
         for (int r = 0; r < p.world; ++r) {
+          if (p.dst_mask != 0u && !((p.dst_mask >> r) & 1u)) continue;
           if (!sharded || r == p.rank) *reinterpret_cast<float4*>(p.params[r] + i) = w;
           if (p.shadow[r]) *reinterpret_cast<uint2*>(p.shadow[r] + i) = wb;
         }
@@ -266,64 +342,152 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
   }
 }
 
-__global__ void __launch_bounds__(256)
+// push, phase 1: my gradients of this block's vectors into my row on every peer
+__device__ __forceinline__ void push_range(const FusedParams& p, long long vec_total, int parity) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long row = ((long long)parity * p.world + p.rank) * p.push_stride;
+  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < vec_total; v += stride) {
+    const float4 g = *reinterpret_cast<const float4*>(p.grads[p.rank] + p.offset + (v << 2));
+    for (int r = 0; r < p.world; ++r)
+      if (r != p.rank) st_peer_f4(p.push_recv[r] + row + (v << 2), g);
+  }
+}
+
+__device__ __forceinline__ unsigned long long tagged(uint32_t tag, float v) {
+  return (static_cast<unsigned long long>(tag) << 32) | __float_as_uint(v);
+}
+
+__global__ void __launch_bounds__(256, 4)
 fused_allreduce_update_kernel(const FusedParams p) {
   const int b = blockIdx.x;
+  const int fb = p.chan_base + b;                    // this block's flag / sequence slot
   __shared__ uint32_t s_seq;
+  __shared__ float s_red[8];
+  __shared__ int s_last;
   pdl_sync();
-  if (threadIdx.x == 0) s_seq = p.seq[b];
+  if (threadIdx.x == 0) s_seq = p.world > 1 ? p.seq[fb] : 0u;
   __syncthreads();
   const uint32_t seq = s_seq;
-  const Hyper h = make_hyper(p);
+  const long long step = p.step_ptr ? *p.step_ptr : 0;
+  const Hyper h = make_hyper(p, step);
   const bool multi = p.world > 1;
-  // every peer's gradients are complete (with pre-reduced ranges some of them were written into MY memory by
-  // peers' kernels: the fence makes this rank's own remote additions globally visible before it signals)
-  if (multi) cross_gpu_barrier(p, b, seq + 1, p.n_prered > 0);
-
+  const bool sliced = multi && (p.algo == 1 || p.algo == 2);
   const long long vec_total = p.count >> 2;
+  float l2 = 0.f;
+  uint32_t rounds = 0;
+
   if (!multi) {
-    run_range<kLocal>(p, h, 0, vec_total);
-  } else if (p.algo == 0) {
-    run_range<kOneShot>(p, h, 0, vec_total);
+    run_range<kLocal>(p, h, 0, vec_total, l2);
+  } else if (p.algo == 3) {
+    // one flag round: data first, then the flag (release after a system fence), then the local reduction
+    const int parity = (int)(step & 1);
+    push_range(p, vec_total, parity);
+    cross_gpu_barrier(p, fb, seq + 1, true);
+    rounds = 1;
+    run_range<kPush>(p, h, 0, vec_total, l2, p.push_recv[p.rank] + (long long)parity * p.world * p.push_stride);
   } else {
-    // two-shot / nvls: this rank owns one contiguous slice
-    const long long per = (vec_total + p.world - 1) / p.world;
-    const long long lo = per * p.rank < vec_total ? per * p.rank : vec_total;
-    const long long hi = lo + per < vec_total ? lo + per : vec_total;
-    if (p.algo == 2) run_range<kNvls>(p, h, lo, hi);
-    else run_range<kTwoShot>(p, h, lo, hi);
+    // every peer's gradients are complete (with pre-reduced ranges some of them were written into MY memory by
+    // peers' kernels: the fence makes this rank's own remote additions globally visible before it signals)
+    cross_gpu_barrier(p, fb, seq + 1, p.n_prered > 0);
+    if (p.algo == 0) {
+      run_range<kOneShot>(p, h, 0, vec_total, l2);
+    } else {
+      // two-shot / nvls: this rank owns one contiguous slice
+      const long long per = (vec_total + p.world - 1) / p.world;
+      const long long lo = per * p.rank < vec_total ? per * p.rank : vec_total;
+      const long long hi = lo + per < vec_total ? lo + per : vec_total;
+      if (p.algo == 2) run_range<kNvls>(p, h, lo, hi, l2);
+      else run_range<kTwoShot>(p, h, lo, hi, l2);
+    }
+    // peers are done reading my grads (loads have retired: their values were consumed) and, in the
+    // two-shot / nvls forms, done writing my params (needs the fence)
+    cross_gpu_barrier(p, fb, seq + 2, p.algo != 0);
+    rounds = 2;
   }
-  // peers are done reading my grads (loads have retired: their values were consumed) and, in the
-  // two-shot / nvls forms, done writing my params (needs the fence)
-  if (multi) cross_gpu_barrier(p, b, seq + 2, p.algo != 0);
+
+  const bool want_l2 = p.l2_blocks != nullptr;
+  if (want_l2) {                                     // block partial, summed in warp order
+    l2 = warp_sum(l2);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = l2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_red[w];
+      p.l2_blocks[b] = t;
+    }
+  }
   if (threadIdx.x == 0) {
-    p.seq[b] = seq + 2;
-    if (p.advance_step != nullptr) {
-      // every block read the step counter at its start; the last one to finish moves it on
+    if (multi) p.seq[fb] = seq + rounds;
+    s_last = 0;
+    if (p.done_counter != nullptr) {
+      // every block read the step counter at its start; the last one to finish closes the launch
       __threadfence();
       if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
         *p.done_counter = 0u;
-        const long long next = *p.advance_step + 1;
-        *p.advance_step = next;
-        if (p.loss_mail != nullptr) {
-          // one 8-byte store = one PCIe write: the host sees the loss and its step number together
-          const unsigned long long word = (static_cast<unsigned long long>(static_cast<uint32_t>(next)) << 32) |
-                                          __float_as_uint(*p.loss_src);
-          asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.loss_mail + ((next - 1) & (p.loss_ring - 1))),
-                       "l"(word) : "memory");
-        }
+        s_last = 1;
       }
+    }
+  }
+  __syncthreads();
+  if (!s_last || threadIdx.x != 0) return;
+  __threadfence();
+  const uint32_t tag = static_cast<uint32_t>(step + 1);
+  if (want_l2) {
+    float total = 0.f;
+    for (int k = 0; k < (int)gridDim.x; ++k) total += __ldcg(p.l2_blocks + k);      // block order: reproducible
+    const unsigned long long word = tagged(tag, total);
+    if (sliced) {                                    // I only walked my slice: every rank needs every partial
+      for (int r = 0; r < p.world; ++r)
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.l2_slots[r] + p.l2_row * kMaxRanks + p.rank), "l"(word)
+                     : "memory");
+    } else {
+      asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.l2_slots[p.rank] + p.l2_row * kMaxRanks), "l"(word)
+                   : "memory");
+    }
+  }
+  if (p.advance_step != nullptr) {
+    const long long next = step + 1;
+    *p.advance_step = next;
+    if (p.loss_mail != nullptr) {
+      float loss = *p.loss_src;
+      if (want_l2) {
+        // partials of this step, mine and the slice owners', in row / rank order; each word carries its step
+        float sum = 0.f;
+        const long long t0 = clock64();
+        for (int row = 0; row < kL2Rows; ++row)
+          for (int e = 0; e < p.l2_rows_n[row]; ++e) {
+            const unsigned long long* src = p.l2_slots[p.rank] + row * kMaxRanks + e;
+            unsigned long long w;
+            while (true) {
+              asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+              if (static_cast<uint32_t>(w >> 32) == tag) break;
+              if (clock64() - t0 > kSpinLimit) { atomicExch(p.status, MTB_E_TIMEOUT); break; }
+            }
+            sum += __uint_as_float(static_cast<uint32_t>(w));
+          }
+        loss = fmaf(p.wd, sum, loss);
+      }
+      // one 8-byte store = one PCIe write: the host sees the value and its step number together
+      const long long slot = (next - 1) & (p.loss_ring - 1);
+      if (p.aux_mail != nullptr && p.err_src != nullptr)
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.aux_mail + slot),
+                     "l"((static_cast<unsigned long long>(tag) << 32) | static_cast<uint32_t>(*p.err_src)) : "memory");
+      asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.loss_mail + slot), "l"(tagged(tag, loss)) : "memory");
     }
   }
 }
 
+// The stand-alone barrier has a flag block of its own (the last one), so it never shares a sequence number with a
+// fused launch that may be in flight on another stream.
+constexpr int kBarrierBlock = kMaxBlocks - 1;
+
 __global__ void barrier_kernel(const FusedParams p) {
   __shared__ uint32_t s_seq;
-  if (threadIdx.x == 0) s_seq = p.seq[0];
+  if (threadIdx.x == 0) s_seq = p.seq[kBarrierBlock];
   __syncthreads();
   const uint32_t seq = s_seq;
-  cross_gpu_barrier(p, 0, seq + 2, true);
-  if (threadIdx.x == 0) p.seq[0] = seq + 2;
+  cross_gpu_barrier(p, kBarrierBlock, seq + 2, true);
+  if (threadIdx.x == 0) p.seq[kBarrierBlock] = seq + 2;
 }
 
 __global__ void advance_step_kernel(long long* step) { *step += 1; }
@@ -336,7 +500,9 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   MTB_REQUIRE(a->world >= 1 && a->world <= kMaxRanks && a->rank >= 0 && a->rank < a->world, "fused: bad world/rank");
   MTB_REQUIRE(a->offset % 4 == 0 && a->count % 4 == 0 && a->count >= 0, "fused: offset/count must be multiples of 4");
   MTB_REQUIRE(a->n_ranges >= 0 && a->n_ranges <= kMaxRanges, "fused: too many decay ranges");
+  MTB_REQUIRE(a->algo >= 0 && a->algo <= 3, "fused: algo must be 0 (one-shot), 1 (two-shot), 2 (nvls) or 3 (push)");
   MTB_REQUIRE(a->algo != 2 || (a->mc_grads && a->mc_params), "fused: nvls needs multicast pointers");
+  MTB_REQUIRE(a->chan == 0 || a->chan == 1, "fused: chan must be 0 or 1");
   p->world = a->world; p->rank = a->rank; p->algo = a->algo; p->optimizer = a->optimizer;
   for (int r = 0; r < kMaxRanks; ++r) {
     p->grads[r] = reinterpret_cast<const float*>(a->grads[r]);
@@ -373,6 +539,39 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->loss_src = reinterpret_cast<const float*>(a->loss_src);
   p->loss_mail = reinterpret_cast<unsigned long long*>(a->loss_mail);
   p->loss_ring = a->loss_ring;
+  p->chan_base = a->chan * kChanBlocks;
+  p->push_stride = a->push_stride;
+  for (int r = 0; r < kMaxRanks; ++r) {
+    p->push_recv[r] = reinterpret_cast<float*>(a->push_recv[r]);
+    p->grads_lp[r] = reinterpret_cast<const __nv_bfloat16*>(a->grads_lp[r]);
+    p->l2_slots[r] = reinterpret_cast<unsigned long long*>(a->l2_slots[r]);
+  }
+  if (a->algo == 3 && a->world > 1) {
+    MTB_REQUIRE(a->push_stride >= a->count && a->push_stride % 4 == 0, "fused: push_stride must cover the bucket");
+    for (int r = 0; r < a->world; ++r) MTB_REQUIRE(a->push_recv[r] != nullptr, "fused: push needs every rank's receive area");
+    MTB_REQUIRE(a->n_prered == 0 && a->lp_end <= a->lp_begin, "fused: push takes plain fp32 gradients");
+  }
+  p->mc_grads_lp = reinterpret_cast<const __nv_bfloat16*>(a->mc_grads_lp);
+  p->lp_begin = a->lp_begin; p->lp_end = a->lp_end;
+  if (a->lp_end > a->lp_begin) {
+    MTB_REQUIRE(a->lp_begin % 4 == 0 && a->lp_end % 4 == 0, "fused: bf16-wire range must be a multiple of 4");
+    for (int r = 0; r < a->world; ++r) MTB_REQUIRE(a->grads_lp[r] != nullptr, "fused: bf16-wire range without bf16 buffers");
+    MTB_REQUIRE(a->algo != 2 || a->world == 1 || a->mc_grads_lp != nullptr, "fused: nvls with a bf16-wire range needs its multicast view");
+  }
+  p->dst_mask = a->dst_mask;
+  MTB_REQUIRE(a->dst_mask == 0u || a->algo == 1, "fused: dst_mask is a two-shot option");
+  p->l2_blocks = reinterpret_cast<float*>(a->l2_blocks);
+  p->l2_row = a->l2_row;
+  for (int r = 0; r < kL2Rows; ++r) p->l2_rows_n[r] = a->l2_rows_n[r];
+  if (p->l2_blocks != nullptr) {
+    MTB_REQUIRE(a->l2_row >= 0 && a->l2_row < kL2Rows, "fused: l2_row out of range");
+    MTB_REQUIRE(p->done_counter != nullptr && p->step_ptr != nullptr, "fused: the L2 value needs done_counter and step_ptr");
+    for (int r = 0; r < a->world; ++r) MTB_REQUIRE(a->l2_slots[r] != nullptr, "fused: the L2 value needs every rank's slots");
+    for (int r = 0; r < kL2Rows; ++r)
+      MTB_REQUIRE(a->l2_rows_n[r] >= 0 && a->l2_rows_n[r] <= a->world, "fused: l2_rows_n out of range");
+  }
+  p->err_src = reinterpret_cast<const int*>(a->err_src);
+  p->aux_mail = reinterpret_cast<unsigned long long*>(a->aux_mail);
   MTB_REQUIRE(p->loss_mail == nullptr || (p->advance_step != nullptr && p->loss_src != nullptr && p->loss_ring > 0 &&
                                           (p->loss_ring & (p->loss_ring - 1)) == 0),
               "fused: loss_mail needs advance_step, loss_src and a power-of-two loss_ring");
@@ -386,18 +585,22 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   MTB_REQUIRE(p.optimizer < 1 || p.slot_m, "fused: momentum/adam need slot_m");
   MTB_REQUIRE(p.optimizer < 2 || p.slot_v, "fused: adam needs slot_v");
   MTB_REQUIRE(p.world == 1 || (p.seq && p.status && p.flags[p.rank]), "fused: multi-GPU needs flags/seq/status");
-  MTB_REQUIRE(p.seq, "fused: seq buffer required");
   if (p.count == 0) return 0;
   // 256-thread blocks without shared memory fit next to the persistent tensor-core kernels, so
   // a bucket's update can run on a second stream underneath the rest of backward
   int block = a->block > 0 ? (a->block > 256 ? 256 : a->block) : 256;
   long long vecs = p.count >> 2;
-  if (p.world > 1 && p.algo != 0) vecs = (vecs + p.world - 1) / p.world;
-  int grid = a->grid > 0 ? a->grid : 3 * 148;
+  if (p.world > 1 && (p.algo == 1 || p.algo == 2)) vecs = (vecs + p.world - 1) / p.world;     // owner slices
+  if (block < 32) block = 32;
+  block = (block + 31) / 32 * 32;
+  // a lone GPU has no flag rounds to pay per block: cover the chip; with peers the blocks of one launch share a
+  // channel of 255 flag blocks
+  int grid = a->grid > 0 ? a->grid : (p.world == 1 ? 3 * 148 : kChanBlocks - 1);
   // one pass = 4 vectors (64 bytes) per thread; another block (and its flag round) pays off after that
   long long need = (vecs + 4 * block - 1) / (4 * block);
   if (need < 1) need = 1;
   if (grid > need) grid = (int)need;
+  if (p.world > 1 && grid > kChanBlocks - 1) grid = kChanBlocks - 1;
   if (grid > kMaxBlocks) grid = kMaxBlocks;
   MTB_CUDA_CHECK(mtb::launch(fused_allreduce_update_kernel, dim3(grid), dim3(block), 0, stream, p));
   return 0;

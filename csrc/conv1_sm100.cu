@@ -447,11 +447,14 @@ conv1_wgrad_tc_kernel(const float* __restrict__ x, const bf16* __restrict__ dP, 
   if (warp == 0) { tc_fence_after(); tmem_dealloc<32>(tmem); }
 }
 
+// The opt-in to more than 48 KB of dynamic shared memory is per device: `done` is indexed by device ordinal.
 template <typename K>
 int set_smem(K kern, int bytes, bool* done) {
-  if (!*done) {
+  int dev = 0;
+  MTB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !done[dev]) {
     MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    *done = true;
+    if (dev >= 0 && dev < 64) done[dev] = true;
   }
   return 0;
 }
@@ -489,8 +492,8 @@ int mtb_conv1_fwd_tc_win_zero(const float* x, const float* w, const float* bias,
   for (int k = 0; k < 8; ++k) { zl.ptr[k] = k < zero_count ? zero_ptrs[k] : nullptr; zl.n_words[k] = k < zero_count ? zero_words[k] : 0; }
   zl.count = zero_count;
   MTB_REQUIRE(win_step == nullptr || win_rows > B, "conv1_fwd_tc: shard must be larger than the batch");
-  static bool attr = false;
-  if (int e = set_smem(conv1_fwd_tc_kernel, f1::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv1_fwd_tc_kernel, f1::kSmem, attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
   MTB_CUDA_CHECK(mtb::launch(conv1_fwd_tc_kernel, dim3(grid), dim3(f1::kThreads), (size_t)f1::kSmem, stream, x, w, bias,
                              reinterpret_cast<bf16*>(out_bf16), idx, B, win_step, win_rows, zl));
@@ -507,8 +510,8 @@ int mtb_conv1_wgrad_tc_win(const float* x, const void* dP_bf16, const void* P_bf
                            float* db, int B, const long long* win_step, long long win_rows, cudaStream_t stream) {
   MTB_REQUIRE(x && dP_bf16 && P_bf16 && idx && dW && db && B > 0, "conv1_wgrad_tc: bad argument");
   MTB_REQUIRE(win_step == nullptr || win_rows > B, "conv1_wgrad_tc: shard must be larger than the batch");
-  static bool attr = false;
-  if (int e = set_smem(conv1_wgrad_tc_kernel, g1::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv1_wgrad_tc_kernel, g1::kSmem, attr)) return e;
   const int grid = B < mtb::kNumSMs ? B : mtb::kNumSMs;
   MTB_CUDA_CHECK(mtb::launch(conv1_wgrad_tc_kernel, dim3(grid), dim3(g1::kThreads), (size_t)g1::kSmem, stream, x,
                              reinterpret_cast<const bf16*>(dP_bf16), reinterpret_cast<const bf16*>(P_bf16), idx, dW, db,

@@ -713,11 +713,14 @@ bool get_map(CUtensorMap* out, const void* p, int B, int kind) {
   return true;
 }
 
+// The opt-in to more than 48 KB of dynamic shared memory is per device: `done` is indexed by device ordinal.
 template <typename K>
 int set_smem(K kern, int bytes, bool* done) {
-  if (!*done) {
+  int dev = 0;
+  MTB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !done[dev]) {
     MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    *done = true;
+    if (dev >= 0 && dev < 64) done[dev] = true;
   }
   return 0;
 }
@@ -735,8 +738,8 @@ int mtb_conv2_fprop_pool(const void* x_bf16, const void* w_bf16, const float* bi
   MTB_REQUIRE(x_bf16 && w_bf16 && bias && out_bf16 && idx && B > 0, "conv2_fprop: bad argument");
   CUtensorMap mx, mw;
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&mw, w_bf16, 0, 3), "conv2_fprop: tensor map encode failed");
-  static bool attr = false;
-  if (int e = set_smem(conv2_fprop_pool_kernel, fp::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv2_fprop_pool_kernel, fp::kSmem, attr)) return e;
   MTB_CUDA_CHECK(mtb::launch(conv2_fprop_pool_kernel, dim3(grid_for(B)), dim3(fp::kThreadsFp), (size_t)fp::kSmem, stream,
                              mx, mw, bias, reinterpret_cast<bf16*>(out_bf16), idx, B));
   return 0;
@@ -746,8 +749,8 @@ int mtb_conv2_dgrad(const void* dy_bf16, const void* w_bf16, void* dx_bf16, int 
   MTB_REQUIRE(dy_bf16 && w_bf16 && dx_bf16 && B > 0, "conv2_dgrad: bad argument");
   CUtensorMap md, mw;
   MTB_REQUIRE(get_map(&md, dy_bf16, B, 1) && get_map(&mw, w_bf16, 0, 3), "conv2_dgrad: tensor map encode failed");
-  static bool attr = false;
-  if (int e = set_smem(conv2_dgrad_kernel<false>, dg::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv2_dgrad_kernel<false>, dg::kSmem, attr)) return e;
   MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<false>, dim3(grid_for(B)), dim3(kThreadsD), (size_t)dg::kSmem, stream, md,
                              mw, reinterpret_cast<bf16*>(dx_bf16), B, PooledGrad{nullptr, nullptr, nullptr}));
   return 0;
@@ -760,8 +763,8 @@ int mtb_conv2_dgrad_unpool(const void* dflat_bf16, const void* pooled_bf16, cons
   MTB_REQUIRE(dflat_bf16 && pooled_bf16 && idx && w_bf16 && dx_bf16 && B > 0, "conv2_dgrad_unpool: bad argument");
   CUtensorMap mw;
   MTB_REQUIRE(get_map(&mw, w_bf16, 0, 3), "conv2_dgrad_unpool: tensor map encode failed");
-  static bool attr = false;
-  if (int e = set_smem(conv2_dgrad_kernel<true>, dg::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv2_dgrad_kernel<true>, dg::kSmem, attr)) return e;
   const PooledGrad pg{reinterpret_cast<const bf16*>(dflat_bf16), reinterpret_cast<const bf16*>(pooled_bf16), idx};
   MTB_CUDA_CHECK(mtb::launch(conv2_dgrad_kernel<true>, dim3(grid_for(B)), dim3(kThreadsD + kBuildersD), (size_t)dg::kSmem,
                              stream, mw, mw, reinterpret_cast<bf16*>(dx_bf16), B, pg));
@@ -777,8 +780,8 @@ int mtb_conv2_wgrad(const void* x_bf16, const void* dy_bf16, float* dW, float* d
   MTB_REQUIRE(x_bf16 && dy_bf16 && dW && db && workspace && B > 0, "conv2_wgrad: bad argument");
   CUtensorMap mx, md;
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0) && get_map(&md, dy_bf16, B, 2), "conv2_wgrad: tensor map encode failed");
-  static bool attr = false;
-  if (int e = set_smem(conv2_wgrad_kernel<false>, wg::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv2_wgrad_kernel<false>, wg::kSmem, attr)) return e;
   const int grid = wgrad_grid(B);
   MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_kernel<false>, dim3(grid), dim3(kThreads), (size_t)wg::kSmem, stream, mx, md,
                              reinterpret_cast<float*>(workspace), db, B, PooledGrad{nullptr, nullptr, nullptr}));
@@ -794,8 +797,8 @@ int mtb_conv2_wgrad_unpool(const void* x_bf16, const void* dflat_bf16, const voi
               "conv2_wgrad_unpool: bad argument");
   CUtensorMap mx;
   MTB_REQUIRE(get_map(&mx, x_bf16, B, 0), "conv2_wgrad_unpool: tensor map encode failed");
-  static bool attr = false;
-  if (int e = set_smem(conv2_wgrad_kernel<true>, wg::kSmem, &attr)) return e;
+  static bool attr[64] = {};
+  if (int e = set_smem(conv2_wgrad_kernel<true>, wg::kSmem, attr)) return e;
   const int grid = wgrad_grid(B);
   const PooledGrad pg{reinterpret_cast<const bf16*>(dflat_bf16), reinterpret_cast<const bf16*>(pooled_bf16), idx};
   MTB_CUDA_CHECK(mtb::launch(conv2_wgrad_kernel<true>, dim3(grid), dim3(kThreads + kBuilders), (size_t)wg::kSmem, stream,

@@ -413,10 +413,13 @@ bool get_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, u
 template <int BN, bool A_MN, bool B_MN, int CM = 1, int CN = 1, bool TF32 = false>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CM, CN, TF32>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the opt-in to more than 48 KB of dynamic shared memory is a per-device property of the function
+  static bool attr_set[64] = {};
+  int dev = 0;
+  MTB_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
-    attr_set = true;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   dim3 grid((unsigned)mtb::ceil_div(p.M, BM), (unsigned)mtb::ceil_div(p.N, BN), (unsigned)p.splits);
   GemmParams q = p;
@@ -663,7 +666,8 @@ int mtb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* out, int M,
   MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm_noalloc: null pointer or empty shape");
   MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm_noalloc: operand row pitch must be a multiple of 16 bytes");
   MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm_noalloc: operands must be 16-byte aligned");
-  if (bn != 64 && bn != 128) bn = 64;
+  if (bn == 0) bn = 64;                                  // 0 = default tile width
+  MTB_REQUIRE(bn == 64 || bn == 128, "gemm_noalloc: bn must be 0 (default), 64 or 128");
   if (splits < 1) splits = 1;
   GemmParams p;
   p.M = M; p.N = N; p.K = K;

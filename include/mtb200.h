@@ -72,7 +72,7 @@ int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int 
  * output; no dropout).  Scratch is a fixed 4 MiB + 4 KiB device array inside the library, one per GPU, kept until
  * exit; shapes whose split-K partials need more return MTB_E_LIMIT.  Allocates nothing.  First call per device
  * resolves the array's address: do it at start-up, before any stream capture.  Calls share the array: never let two
- * of them overlap on one GPU. */
+ * of them overlap on one GPU.  bn: 0 (= 64), 64 or 128; anything else is MTB_E_ARG. */
 size_t mtb_gemm_noalloc_max_workspace_bytes(void);
 int mtb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* out, int M, int N, int K, int a_mn_major,
                                  int b_mn_major, long long lda, long long ldb, long long ldc, int out_bf16,
@@ -228,6 +228,30 @@ typedef struct mtb_fused_args {
    * The owner reads them locally instead of reducing over peers and zeroes them for the next step. */
   int n_prered;
   long long prered_begin[2], prered_end[2];
+  /* Launches that may be in flight at the same time (a bucket on a communication stream under the rest of backward, the
+   * closing bucket on the main stream) must use different channels: each has its own flag and sequence blocks. */
+  int chan;             /* 0 or 1 */
+  /* algo 3, "push": one-shot for a small bucket with ONE flag round.  Every rank stores its gradients into its row of
+   * each peer's receive area (rows double buffered by the parity of *step_ptr), signals, and reduces its local rows. */
+  void* push_recv[16];  /* every rank's receive area, peer-mapped: [2][world][push_stride] floats */
+  long long push_stride;/* floats per row, >= count, multiple of 4 */
+  /* bf16 gradient wire format: inside [lp_begin, lp_end) gradients are read as bf16 from grads_lp (peer loads, or
+   * multimem.ld_reduce with fp32 accumulation in the switch) and everything after the load stays fp32. */
+  const void* grads_lp[16];
+  const void* mc_grads_lp;
+  long long lp_begin, lp_end;
+  unsigned dst_mask;    /* two-shot only: bit r set = rank r receives the result; 0 = every rank.  Bit 0 alone is the
+                         * reference's root-only assign (mpipy.py:129) when the kernel averages parameters. */
+  /* L2 term of the loss (mpipy.py:57-58): with l2_blocks set the launch sums 0.5*w^2 (weights before the update) over the
+   * range_* it walks and stores {step+1 : value} into row l2_row of the slots (its own entry on every rank when it only
+   * walked an owner slice, entry 0 locally otherwise).  The launch that mails the loss adds wd * (all entries listed in
+   * l2_rows_n) to *loss_src.  Needs done_counter and step_ptr. */
+  void* l2_blocks;      /* float[grid] scratch, one per channel */
+  void* l2_slots[16];   /* every rank's uint64[4][16], peer-mapped */
+  int l2_row;
+  int l2_rows_n[4];     /* entries to add per row: 0 unused, 1 local, world = one per slice owner */
+  const void* err_src;  /* int32 error count of the batch, mailed as {step : errors} into aux_mail (same ring size) */
+  void* aux_mail;
 } mtb_fused_args;
 int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
 int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */

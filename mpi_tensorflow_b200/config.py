@@ -46,16 +46,17 @@ class TrainConfig:
     sync_include_bias: bool = True      # reference: False (bias lines commented, mpipy.py:122-128)
     sync_include_momentum: bool = False
     sync_root_only: bool = False        # True reproduces mpipy.py:129 (mean stays on root)
-    comm_algo: str = "auto"             # auto | oneshot | twoshot | nvls | nccl (baseline)
+    comm_algo: str = "auto"             # auto | oneshot | twoshot | nvls | push (closing bucket only) | nccl (baseline)
     fuse_wgrad_rs: bool = False         # FC1 weight gradient: GEMM -> reduce-scatter in one kernel (tiles added into the
                                         # owner rank's slice over NVLink); K1 then skips that range's peer reduction
-    comm_dtype: str = "fp32"            # gradient wire format; only fp32 is implemented (bf16 is rejected)
+    comm_dtype: str = "fp32"            # gradient wire format: fp32, or bf16 for the FC1 weight gradient (98 % of the
+                                        # bytes; fp32 accumulation in K1 / in the switch, needs dtype="bf16")
     shard_master: bool = True           # two-shot / nvls: the big weights' fp32 master stays with the slice owner,
                                         # only their bf16 shadow is broadcast (gathered on demand for checkpoints)
     backend: str = "auto"               # auto | p2p | nccl | gloo | shm | self
     device: str = "auto"                # auto | cuda | cpu
-    overlap: bool = False               # fc-bucket allreduce+update on a comm stream under the conv backward
-                                        # (measured slower than the single launch on 2 and 8 B200s: off)
+    overlap: bool = True                # bucketed K1: the fc bucket's allreduce+update (narrow blocks, comm stream) hides
+                                        # under the conv backward; a few-KB "push" bucket with one flag round closes the step
     # eval / logging
     eval_every: int = 50                # reference: 1 (mpipy.py:86)
     eval_dropout: bool = False          # reference: True (mpipy.py:166 via :68)
@@ -63,6 +64,8 @@ class TrainConfig:
     log_every: int = 50                 # mpipy.py:87
     log_jsonl: Optional[str] = None
     log_all_ranks: bool = False
+    profile_phases: bool = False        # at every log line, run one step eagerly with CUDA events between its phases
+                                        # (fwd / bwd / allreduce+update) and add their times and the bus GB/s to the line
     # runtime
     conv_impl: str = "auto"             # auto | implicit (shift-GEMM, no im2col) | im2col (+ GEMM)
     cuda_graph: bool = True

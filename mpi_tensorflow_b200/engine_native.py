@@ -41,10 +41,12 @@ class NativeEngine:
         if device.type != "cuda":
             raise RuntimeError("NativeEngine needs a CUDA device")
         N.lib()                                   # fail loudly if the extension is missing
-        if cfg.comm_dtype != "fp32":
-            raise NotImplementedError("comm_dtype='bf16' is not implemented: gradients cross NVLink in fp32")
+        if cfg.comm_dtype not in ("fp32", "bf16"):
+            raise ValueError(f"comm_dtype must be 'fp32' or 'bf16', got {cfg.comm_dtype!r}")
         if cfg.dtype not in ("bf16", "fp32"):
             raise ValueError(f"dtype must be 'bf16' or 'fp32', got {cfg.dtype!r}")
+        if cfg.comm_dtype == "bf16" and cfg.dtype != "bf16":
+            raise ValueError("comm_dtype='bf16' (bf16 gradients on the wire) needs dtype='bf16'")
         # fp32: every activation, weight operand and gradient is fp32; the GEMM-shaped products run as TF32
         # tensor-core MMAs with fp32 accumulation, conv1 (K = 25) and the loss head on fp32 CUDA cores.
         self.fp32 = cfg.dtype == "fp32"
@@ -64,7 +66,10 @@ class NativeEngine:
         # GEMM -> reduce-scatter for the FC1 weight gradient (cfg.fuse_wgrad_rs): needs peers, an owner-sliced K1
         # over the whole buffer (so the GEMM and K1 agree on who owns what) and the bf16 GEMM engine
         self._rs_mode = (bool(cfg.fuse_wgrad_rs) and self.p2p is not None and self.world > 1 and not self.fp32
-                         and not cfg.overlap and cfg.comm_algo != "oneshot")
+                         and cfg.comm_algo not in ("oneshot", "push") and not self._lp)
+        # bucketed overlap (default): the fc bucket's fused allreduce+update runs on the comm stream under the
+        # convolution backward; the reduce-scatter GEMM needs the single whole-buffer launch instead
+        self._overlap = bool(cfg.overlap) and not self._rs_mode
         self._rs_active = False                  # True only inside the fused step body
         self._rs_dirty = True                    # owners' fc1 slices must be zero when a fused step starts
         if self._rs_mode:
@@ -86,7 +91,10 @@ class NativeEngine:
         self.decay_rows = cfg.lr_decay_rows
         self._side = torch.cuda.Stream(device=device)
         self._comm_stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("MTB_COMM_PRIO", "-1")))
-        self._ev_fc, self._ev_done = torch.cuda.Event(), torch.cuda.Event()
+        self._ev_fc, self._ev_c2, self._ev_done = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+        self._eval_cache: Dict = {}
+        self._marks = None                       # list of (name, event) while a step is being phase-timed
+        self._nvtx = os.environ.get("MTB_NVTX") == "1"
         self.last_aux: Dict = {}
 
     # ------------------------------------------------------------------ buffers
@@ -109,11 +117,35 @@ class NativeEngine:
         raw, self._shadow_ptrs, self._shadow_mc = self._sym(n * 2)
         self.shadow = raw[:n * 2].view(torch.bfloat16)
         self.has_nvls = bool(self._param_mc and self._grad_mc and self._shadow_mc)
+        multi = self.p2p is not None and self.world > 1
+        # bf16 gradient wire format (cfg.comm_dtype="bf16"): the FC1 weight gradient (98 % of the bytes) is stored
+        # as bf16 by its GEMM's epilogue into a second symmetric bucket and crosses NVLink at 2 bytes per element
+        self._lp = self.cfg.comm_dtype == "bf16"
+        self.flat_grads_lp = None
+        if self._lp:
+            raw, self._grad_lp_ptrs, self._grad_lp_mc = self._sym(n * 2)
+            self.flat_grads_lp = raw[:n * 2].view(torch.bfloat16)
+            self.has_nvls = self.has_nvls and bool(self._grad_lp_mc)
+        # optimizer slots are peer-mapped only when the sync strategy averages them (weight_avg + include_momentum)
+        sym_slots = multi and self.cfg.sync == "weight_avg" and self.cfg.sync_include_momentum
         self.slots: List[torch.Tensor] = []
-        if self.cfg.optimizer in ("momentum", "adam"):
-            self.slots.append(torch.zeros(n, device=dev))
-        if self.cfg.optimizer == "adam":
-            self.slots.append(torch.zeros(n, device=dev))
+        self._slot_ptrs, self._slot_mc = [], []
+        n_slots = {"momentum": 1, "adam": 2}.get(self.cfg.optimizer, 0)
+        for _ in range(n_slots):
+            if sym_slots:
+                raw, ptrs, mc = self._sym(n * 4)
+                self.slots.append(raw[:n * 4].view(torch.float32))
+                self._slot_ptrs.append(ptrs)
+                self._slot_mc.append(mc)
+            else:
+                self.slots.append(torch.zeros(n, device=dev))
+        # receive rows of the "push" tail bucket: [2 parity][world][stride] floats on every rank
+        self._tail_hi = self.spec.param("fc1_weight").offset
+        self._push_stride = (self._tail_hi + 3) // 4 * 4
+        self._push = self.p2p.alloc_symmetric(2 * self.world * self._push_stride * 4) if multi else None
+        self._sliced: Dict = {}                  # (lo, hi) of every owner-sliced peer launch -> algo
+        self._l2_blocks = torch.zeros(2, 512, device=dev)
+        self._l2_slots = torch.zeros(4 * 16, dtype=torch.int64, device=dev)          # world-1 stand-in for the p2p slots
         self.dev_step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.loss_acc = torch.zeros(1, device=dev)
         self.err_acc = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -123,14 +155,19 @@ class NativeEngine:
         # fp32 path: consumers read the fp32 master itself, so every rank needs all of it
         self._shard_master = (bool(self.cfg.shard_master) and self.p2p is not None and self.world > 1
                               and not self.fp32)
-        self._done = torch.zeros(1, dtype=torch.int32, device=dev)
-        # loss mailbox: K1's last block stores {step, loss} words straight into this pinned host ring
+        self._done = torch.zeros(2, dtype=torch.int32, device=dev)                  # one per channel
+        # loss mailbox: K1's last block stores {step, loss} words straight into this pinned host ring, and the
+        # batch's error count into a second one
         self._mail = torch.zeros(self._MAIL_RING, dtype=torch.int64).pin_memory()
         self._mail_np = self._mail.numpy()
+        self._aux = torch.zeros(self._MAIL_RING, dtype=torch.int64).pin_memory()
+        self._aux_np = self._aux.numpy()
         self._seq = torch.zeros(N.lib().mtb_fused_max_blocks(), dtype=torch.int32, device=dev)
         self._status = torch.zeros(1, dtype=torch.int32, device=dev)
         self.P = {p.key: self.flat_params[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
         self.G = {p.key: self.flat_grads[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
+        self.Glp = ({p.key: self.flat_grads_lp[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
+                    if self._lp else None)
         self.S = {p.key: self.shadow[p.offset:p.offset + p.numel].view(p.shape) for p in self.spec.params}
         # ranges that must start each step at zero because their wgrad kernels accumulate
         fc1w = self.spec.param("fc1_weight")
@@ -203,22 +240,38 @@ class NativeEngine:
         torch.cuda.current_stream().synchronize()
 
     # -- state that the two-shot / nvls update keeps only with the owner of each slice ------------
-    def _owned(self):
-        """Element range [lo, hi) of the flat buffers this rank owns in a whole-buffer K1 launch."""
-        vecs = self.n // 4
-        per = (vecs + self.world - 1) // self.world
-        lo = min(per * self.p2p.rank, vecs) * 4
-        return lo, min(lo + per * 4, self.n)
+    def _owned_ranges(self):
+        """Element ranges of the flat buffers whose optimizer state (and sharded fp32 master) only THIS rank
+        maintains: its slice of every owner-sliced K1 launch made so far.  The kernel slices each launch's own
+        [lo, hi) (``allreduce_fused.cu``: ``per = ceil(vectors / world)``), so with bucketed launches ownership is
+        per bucket, not a slice of the whole buffer."""
+        out = []
+        for (lo, hi) in sorted(self._sliced):
+            vecs = (hi - lo) // 4
+            per = (vecs + self.world - 1) // self.world
+            olo = lo + min(per * self.p2p.rank, vecs) * 4
+            out.append((olo, min(olo + per * 4, hi)))
+        return out
 
     def _gather_owned(self, buf: torch.Tensor, ranges):
-        """Make ``buf`` complete on every rank: each rank contributes its owned part of every range
-        (zero elsewhere) and the parts are summed.  Collective; used at checkpoint / inspection time."""
-        olo, ohi = self._owned()
+        """Make ``buf`` complete on every rank.  Inside owner-sliced buckets each rank contributes the part it owns;
+        everything else (buckets every rank updates in full) comes from rank 0.  Parts are summed, so every element
+        has exactly one contributor.  Collective; used at checkpoint / inspection time."""
+        owned = self._owned_ranges()
+        sliced = sorted(self._sliced)
         for lo, hi in ranges:
             seg = torch.zeros(hi - lo, device=self.device)
-            a, b = max(lo, olo), min(hi, ohi)
-            if b > a:
-                seg[a - lo:b - lo] = buf[a:b]
+            for olo, ohi in owned:
+                a, b = max(lo, olo), min(hi, ohi)
+                if b > a:
+                    seg[a - lo:b - lo] = buf[a:b]
+            if self.p2p.rank == 0:                        # the complement of the sliced buckets
+                cur = lo
+                for blo, bhi in sliced + [(hi, hi)]:
+                    a, b = max(cur, lo), min(blo, hi)
+                    if b > a:
+                        seg[a - lo:b - lo] = buf[a:b]
+                    cur = max(cur, bhi)
             self.p2p.allreduce(seg, average=False)
             buf[lo:hi] = seg
 
@@ -263,6 +316,7 @@ class NativeEngine:
         self.params_changed()
         self.synchronize()
         self._mail.zero_()                        # a rewound counter must not match losses mailed before
+        self._aux.zero_()
 
     # ------------------------------------------------------------------ data
     def attach_dataset(self, shards):
@@ -400,10 +454,13 @@ class NativeEngine:
             # ... added tile by tile into the slice owners' buckets over NVLink: the reduce-scatter half of the
             # gradient allreduce happens inside this GEMM, K1 only updates and broadcasts (prered range)
             N.gemm_bf16_rs(flat, self.dh, s.flat_dim, s.fc, B, True, True, s.fc, wbn, self._rs)
+        elif self._lp:
+            # bf16 wire format: the epilogue rounds once and K1 reads 2 bytes per element from every peer
+            gemm(flat, self.dh, self.Glp["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=wbn)
         else:
             gemm(flat, self.dh, G["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=wbn)
 
-    def _backward_conv(self, B: int):
+    def _backward_conv(self, B: int, after_conv2_wgrad=None):
         s = self.spec
         P, G = self.P, self.G
         S = self.P if self.fp32 else self.S
@@ -415,6 +472,8 @@ class NativeEngine:
             N.call("mtb_conv2_wgrad_unpool", self.a1p.data_ptr(), self.dflat.data_ptr(), self.a2p.data_ptr(),
                    self.idx2.data_ptr(), G["conv2_weight"].data_ptr(), G["conv2_bias"].data_ptr(),
                    self.c2_ws.data_ptr(), B)
+            if after_conv2_wgrad is not None:
+                after_conv2_wgrad()
             N.call("mtb_conv2_dgrad_unpool", self.dflat.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(),
                    S["conv2_weight"].data_ptr(), self.dp1.data_ptr(), B)
         else:
@@ -426,6 +485,8 @@ class NativeEngine:
             # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
             gemm(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
                  splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
+            if after_conv2_wgrad is not None:
+                after_conv2_wgrad()
             # conv2 dgrad: dcol = da2 W2^T, then col2im
             gemm(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
             N.call("mtb_col2im_5x5" + sfx, self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
@@ -473,8 +534,15 @@ class NativeEngine:
             a = self.p2p.fused_args()
             for r in range(self.world):
                 a.grads[r], a.params[r], a.shadow[r] = self._grad_ptrs[r], self._param_ptrs[r], self._shadow_ptrs[r]
+                if self._lp:
+                    a.grads_lp[r] = self._grad_lp_ptrs[r]
+                if self._push is not None:
+                    a.push_recv[r] = self._push.ptrs[r]
+            a.push_stride = self._push_stride
             if self.has_nvls:
                 a.mc_grads, a.mc_params, a.mc_shadow = self._grad_mc, self._param_mc, self._shadow_mc
+                if self._lp:
+                    a.mc_grads_lp = self._grad_lp_mc
             if self.fp32:                          # no bf16 shadow on the fp32 path
                 for r in range(self.world):
                     a.shadow[r] = None
@@ -485,8 +553,14 @@ class NativeEngine:
             a.world, a.rank = 1, 0
             a.grads[0], a.params[0], a.shadow[0] = (self.flat_grads.data_ptr(), self.flat_params.data_ptr(),
                                                     None if self.fp32 else self.shadow.data_ptr())
+            if self._lp:
+                a.grads_lp[0] = self.flat_grads_lp.data_ptr()
+            a.l2_slots[0] = self._l2_slots.data_ptr()
             a.seq, a.status = self._seq.data_ptr(), self._status.data_ptr()
             a.scale = 1.0
+        if self._lp:
+            fc1w = s.param("fc1_weight")
+            a.lp_begin, a.lp_end = fc1w.offset, fc1w.offset + fc1w.numel
         a.optimizer = _OPT[c.optimizer]
         a.slot_m = self.slots[0].data_ptr() if self.slots else None
         a.slot_v = self.slots[1].data_ptr() if len(self.slots) > 1 else None
@@ -505,16 +579,25 @@ class NativeEngine:
                 a.shard_begin[i], a.shard_end[i] = p.offset, p.offset + p.numel
         return a
 
-    def _pick_algo(self, count: int) -> int:
+    def _pick_algo(self, count: int, tail: bool = False) -> int:
+        """0 one-shot, 1 two-shot, 2 nvls, 3 push.  ``tail``: the bucket that closes the step on the main stream."""
         algo = self.cfg.comm_algo
         if self.world == 1 or algo == "oneshot":
             return 0
+        push_ok = tail and self._push is not None and count <= self._push_stride and not self._rs_active
+        if algo == "push":
+            if push_ok:
+                return 3
+            algo = "auto"
         if algo == "twoshot":
             return 1
         if algo == "nvls":
             if not self.has_nvls:
                 raise RuntimeError("comm_algo='nvls' but no multicast mapping is available on this box")
             return 2
+        # The closing bucket is exposed (nothing runs under it): stores + ONE flag round beat load-based one-shot's two
+        if push_ok and count * 4 <= (4 << 20):
+            return 3
         # measured crossovers (bench/allreduce_sweep.py, profiles/allreduce_sweep_*.jsonl): below
         # 256 KB one flag round less wins; the in-switch reduction wins from 4 GPUs up, with 2 GPUs
         # it has nothing to save and the plain two-shot is faster
@@ -524,26 +607,44 @@ class NativeEngine:
         return 2 if (self.has_nvls and self.world >= 4 and count * 4 <= (512 << 20)) else 1
 
     def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
-                advance: bool = True, grid: int = 0):
-        """K1 over elements [lo, hi) of the flat buffers; ``advance`` also bumps the step counter."""
+                advance: bool = True, grid: int = 0, block: int = 0, chan: int = 0, l2_row: int = 0,
+                l2_rows=None, tail: bool = False):
+        """K1 over elements [lo, hi) of the flat buffers.  ``advance``: this launch closes the step (bumps the
+        counter, mails loss + error count).  ``l2_row``: where its 0.5*sum(w^2) partial goes; ``l2_rows``: for the
+        closing launch, {row: sliced?} of every launch of the step (its own included)."""
         hi = self.n if hi is None else hi
+        peers = peers and self.p2p is not None and self.world > 1
         a = self._fused_args(peers, lr_override)
         a.offset, a.count = lo, hi - lo
-        a.algo = self._pick_algo(hi - lo) if peers else 0
-        if a.algo == 0:
-            a.n_sharded = 0                                            # one-shot: every rank computes everything
-        elif peers and self.world > 1:
+        a.algo = self._pick_algo(hi - lo, tail) if peers else 0
+        sliced = peers and a.algo in (1, 2)
+        if not sliced:
+            a.n_sharded = 0                                            # every rank computes everything
+        else:
+            self._sliced[(lo, hi)] = a.algo
             self._masters_dirty = self._masters_dirty or a.n_sharded > 0
             self._slots_dirty = True                                   # slots of non-owned slices are not maintained
-        a.grid = grid
-        if self._rs_active and peers and a.algo != 0:
+        a.grid, a.block, a.chan = grid, block, chan
+        if self._rs_active and sliced:
             fc1w = self.spec.param("fc1_weight")
             a.n_prered = 1
             a.prered_begin[0], a.prered_end[0] = fc1w.offset, fc1w.offset + fc1w.numel
+        if a.algo == 3:
+            a.lp_begin = a.lp_end = 0                                  # the tail holds no bf16-wire tensor
+        want_l2 = bool(self.cfg.weight_decay) and lr_override < 0
+        if want_l2:
+            a.l2_blocks, a.l2_row = self._l2_blocks[chan].data_ptr(), l2_row
+            a.done_counter = self._done[chan:].data_ptr()
         if advance:                                                     # iter_ += 1 in the same launch
-            a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done.data_ptr()
+            a.advance_step, a.done_counter = self.dev_step.data_ptr(), self._done[chan:].data_ptr()
             a.loss_src, a.loss_mail, a.loss_ring = self.loss_acc.data_ptr(), self._mail.data_ptr(), self._MAIL_RING
+            a.err_src, a.aux_mail = self.err_acc.data_ptr(), self._aux.data_ptr()
+            if want_l2:
+                rows = l2_rows if l2_rows is not None else {l2_row: sliced}
+                for row, is_sliced in rows.items():
+                    a.l2_rows_n[row] = self.world if (is_sliced and peers) else 1
         N.call("mtb_fused_allreduce_update", C.byref(a))
+        return sliced
 
     # ------------------------------------------------------------------ engine interface
     def compute_grads(self, x, y, step: int) -> float:
@@ -599,39 +700,138 @@ class NativeEngine:
                 if now - t0 > timeout:
                     raise RuntimeError(f"step {step_no}: no loss arrived from the device within {timeout:.0f}s")
 
-    def _step_body(self):
+    def _mark(self, name: str, stream=None):
+        """Phase boundary: an NVTX marker (MTB_NVTX=1, eager steps) and, while :meth:`timed_step` runs, a CUDA event
+        on the stream the phase was launched on."""
+        if self._nvtx and not torch.cuda.is_current_stream_capturing():
+            torch.cuda.nvtx.mark(name)
+        if self._marks is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream if stream is not None else torch.cuda.current_stream())
+            self._marks.append((name, ev))
+
+    def timed_step(self, images=None, labels=None, peers: bool = True) -> Dict[str, float]:
+        """One REAL optimizer step run eagerly with CUDA events between its phases (fwd, bwd,
+        allreduce, update timers).  Returns microseconds: ``fwd``, ``bwd_fc``, ``bwd_conv``, ``k1_hidden`` (the fc
+        bucket's fused allreduce+update, measured on the comm stream where it overlaps ``bwd_conv``), ``k1_tail`` (the
+        exposed closing bucket), ``step``, plus ``allreduce_bytes`` and ``bus_gbs`` = 2(N-1)/N * bytes / (k1_hidden +
+        k1_tail).  Collective when ``peers``: every rank must call it for the same step."""
+        if images is not None:
+            self.stage_batch(images, labels)
+            mode = "staged"
+        elif self._can_window and self.data_x is not None:
+            mode = "window"
+        else:
+            self._window()
+            mode = "staged"
+        self._windowed = mode == "window"
+        self._stream_buf = None
+        peers = peers and self.p2p is not None and self.world > 1
+        if self._rs_mode and self._rs_dirty and peers:
+            self.G["fc1_weight"].zero_()
+            torch.cuda.synchronize()
+            self.p2p.barrier()
+            self._rs_dirty = False
+        self._marks = []
+        try:
+            self._mark("start")
+            self._step_body(peers)
+            self._mark("end")
+            torch.cuda.synchronize()
+            ev = dict(self._marks)
+        finally:
+            self._marks = None
+        self.opt_step += 1
+        us = lambda a, b: ev[a].elapsed_time(ev[b]) * 1e3 if (a in ev and b in ev) else 0.0   # noqa: E731
+        out = {"fwd": us("start", "fwd"), "step": us("start", "end")}
+        if "bwd_fc" in ev:
+            out.update(bwd_fc=us("fwd", "bwd_fc"), bwd_conv=us("bwd_fc", "bwd_conv"),
+                       k1_hidden=us("k1_hidden_begin", "k1_hidden_end"), k1_tail=us("bwd_conv", "end"))
+        else:
+            out.update(bwd=us("fwd", "bwd"), k1_tail=us("bwd", "end"), k1_hidden=0.0)
+        nbytes = self.n * (2 if self._lp else 4)
+        t = out["k1_hidden"] + out["k1_tail"]
+        out["allreduce_bytes"] = nbytes
+        out["bus_gbs"] = (2 * (self.world - 1) / self.world * nbytes / (t * 1e-6) / 1e9) if (peers and t > 0) else 0.0
+        return out
+
+    def _hidden_launch(self, peers: bool, lo: int, hi: int, row: int) -> bool:
+        """One bucket's fused allreduce+update on the comm stream: narrow blocks (128 threads, 64 registers) that fit
+        on an SM NEXT TO the persistent convolution-backward CTAs, a grid sized for the bytes, channel 0."""
+        multi = peers and self.p2p is not None and self.world > 1
+        grid = int(os.environ.get("MTB_K1_GRID_A", "96" if multi else "148"))
+        block = int(os.environ.get("MTB_K1_BLOCK_A", "128"))
+        with torch.cuda.stream(self._comm_stream):
+            if row == 0:
+                self._mark("k1_hidden_begin")
+            sliced = self._update(peers=peers, lo=lo, hi=hi, advance=False, grid=grid, block=block, chan=0, l2_row=row)
+            self._mark("k1_hidden_end")
+        return sliced
+
+    def train_errors(self, step_no: int, timeout: Optional[float] = None) -> int:
+        """Misclassified rows of the batch of optimizer step ``step_no`` (1-based), from the second mailbox ring:
+        the train error the reference computes and throws away (``mpipy.py:89``)."""
+        slot, want = (step_no - 1) % self._MAIL_RING, step_no & 0xFFFFFFFF
+        timeout = float(self.cfg.step_timeout_s) if timeout is None else timeout
+        t0 = time.monotonic()
+        while True:
+            word = int(self._aux_np[slot])
+            if (word >> 32) & 0xFFFFFFFF == want:
+                return int(word & 0xFFFFFFFF)
+            if time.monotonic() - t0 > timeout:
+                raise RuntimeError(f"step {step_no}: no error count arrived from the device within {timeout:.0f}s")
+
+    def _step_body(self, peers: bool = True):
         if self.conv1_tc:
             self._forward(self.B, True, True, zero=True)
         else:
             self._zero_step_accumulators()
             self._forward(self.B, True, True)
-        if not self.cfg.overlap:
-            self._rs_active = self._rs_mode
+        self._mark("fwd")
+        if not self._overlap:
+            self._rs_active = self._rs_mode and peers
             try:
                 self._backward(self.B)
-                self._update(peers=True)
+                self._mark("bwd")
+                self._update(peers=peers, tail=True)
             finally:
                 self._rs_active = False
             return
-        # Two buckets in gradient-ready order (SURVEY 5.5 "Overlap"): the fc bucket (98% of the
-        # bytes) closes first and its fused allreduce+update runs on the comm stream underneath the
-        # convolution backward; the small conv bucket follows on the main stream.
+        # Buckets in gradient-ready order (SURVEY 5.5 "Overlap").  The fc bucket (98% of the bytes) closes after the
+        # FC1 weight gradient; its allreduce+update (both flag rounds included) hides under the convolution backward.
+        # A conv2 bucket follows the same way when it is big (the widened model).  What is left for the end of the
+        # step is a few KB: one launch, one flag round (push), which also advances the step and mails the loss.
         main = torch.cuda.current_stream()
+        comm = self._comm_stream
         split = self.spec.param("fc1_weight").offset
+        c2 = self.spec.param("conv2_weight").offset
+        rows = {}
         self._backward_fc(self.B)
+        self._mark("bwd_fc")
         self._ev_fc.record(main)
-        self._comm_stream.wait_event(self._ev_fc)
-        with torch.cuda.stream(self._comm_stream):
-            self._update(peers=True, lo=split, hi=self.n, advance=False,
-                         grid=int(os.environ.get("MTB_K1_GRID_A", "148")))
-            self._ev_done.record(self._comm_stream)
-        self._backward_conv(self.B)
+        comm.wait_event(self._ev_fc)
+        rows[0] = self._hidden_launch(peers, split, self.n, 0)
+        tail_hi = split
+        hook = None
+        big_conv2 = (split - c2) * 4 > int(os.environ.get("MTB_CONV2_BUCKET_BYTES", str(256 << 10)))
+        if big_conv2:
+            def hook():
+                self._ev_c2.record(main)
+                comm.wait_event(self._ev_c2)
+                rows[1] = self._hidden_launch(peers, c2, split, 1)
+            tail_hi = c2
+        self._backward_conv(self.B, hook)
+        self._mark("bwd_conv")
+        self._ev_done.record(comm)
         main.wait_event(self._ev_done)
-        self._update(peers=True, lo=0, hi=split, advance=True)
+        rows[2] = False                                       # the tail: every rank updates all of it
+        self._update(peers=peers, lo=0, hi=tail_hi, advance=True, chan=1, l2_row=2, l2_rows=rows, tail=True)
 
-    def fused_step(self, images, labels, lr, step: int, read_loss: bool = True):
+    def fused_step(self, images, labels, lr, step: int, read_loss: bool = True, peers: bool = True):
         """One full step: (window | staged batch) -> graph replay.  ``lr`` is ignored: the
-        schedule runs on the device from the device step counter."""
+        schedule runs on the device from the device step counter.  ``peers=False``: a LOCAL step
+        (same graph, K1 without the cross-GPU reduction) - what runs between two parameter averagings of the
+        reference's strategy (mpipy.py:83-91) and under ``sync="none"``."""
         if images is not None:
             self.stage_batch(images, labels)
             mode = "staged"
@@ -642,12 +842,13 @@ class NativeEngine:
         else:
             self._window()
             mode = "staged"
-        self._run_step(mode)
+        self._run_step(mode, peers)
         self.opt_step += 1
         return self._await_loss(self.opt_step) if read_loss else 0.0
 
-    def _run_step(self, mode: str):
-        if self._rs_mode and self._rs_dirty:
+    def _run_step(self, mode: str, peers: bool = True):
+        peers = peers and self.p2p is not None and self.world > 1
+        if self._rs_mode and self._rs_dirty and peers:
             # an eager backward (compute_grads) stored a whole local gradient: put the owners' slices back to zero
             self.G["fc1_weight"].zero_()
             torch.cuda.synchronize()
@@ -656,14 +857,16 @@ class NativeEngine:
         self._windowed = mode == "window"
         self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
         if self.cfg.cuda_graph:
-            if mode not in self._graphs:
-                self._capture(mode)
-            self._graphs[mode].replay()
+            key = mode if peers or self.world == 1 else mode + "/local"
+            if key not in self._graphs:
+                self._capture(mode, peers, key)
+            self._graphs[key].replay()
         else:
-            self._step_body()
+            self._step_body(peers)
 
     # ------------------------------------------------------------------ host-streamed training
-    def stream_steps(self, hx: torch.Tensor, hy: torch.Tensor, steps: int, ring: int = 4) -> List[float]:
+    def stream_steps(self, hx: torch.Tensor, hy: torch.Tensor, steps: int, ring: int = 4,
+                     peers: bool = True) -> List[float]:
         """``steps`` optimizer steps over a dataset that lives in PINNED HOST memory
         (``hx`` [rows, 784] fp32, ``hy`` [rows] int32), walked with the reference's sequential
         window (``mpipy.py:80-82``).  This is the reference's feed loop (``mpipy.py:83-85``: one
@@ -678,8 +881,8 @@ class NativeEngine:
         if hy.dtype != torch.int32 or hx.dtype != torch.float32:
             raise ValueError("stream_steps needs float32 images and int32 labels")
         hx = hx.view(hx.shape[0], -1)
-        nwin = hx.shape[0] // B
-        if nwin < 1:
+        rows = hx.shape[0]
+        if rows < B:
             raise ValueError("dataset smaller than one batch")
         if self._stream_state is None:
             self._stream_state = dict(
@@ -700,7 +903,8 @@ class NativeEngine:
         first = self.opt_step + 1
         for i in range(steps):
             k = i & 1
-            o = (i % nwin) * B
+            # the reference's window, on the GLOBAL step so that a resumed or continued run walks on (mpipy.py:80-82)
+            o = ((self.opt_step * B) % (rows - B)) if rows > B else 0
             copy.wait_event(st["consumed"][k])                 # the step that used this half has copied it out
             with torch.cuda.stream(copy):
                 st["x"][k].copy_(hx[o:o + B], non_blocking=True)
@@ -708,11 +912,11 @@ class NativeEngine:
                 st["ready"][k].record(copy)
             main.wait_event(st["ready"][k])
             if direct:                                         # one graph per half: no device-to-device copy
-                self._run_step(f"stream{k}")
+                self._run_step(f"stream{k}", peers)
             else:
                 self.x_in[:B].copy_(st["x"][k], non_blocking=True)
                 self.y_in[:B].copy_(st["y"][k], non_blocking=True)
-                self._run_step("staged")
+                self._run_step("staged", peers)
             st["consumed"][k].record(main)
             self.opt_step += 1
             if i >= ring:                                      # the device mailed it `ring` steps ago
@@ -721,16 +925,17 @@ class NativeEngine:
             losses.append(self._await_loss(first + len(losses)))
         return losses
 
-    def _capture(self, mode: str = "staged"):
+    def _capture(self, mode: str = "staged", peers: bool = True, key: Optional[str] = None):
         """Warm up eagerly (sets kernel attributes, builds tensor maps), roll the state back, capture.
         One graph per input mode: ``staged`` reads the batch buffers, ``window`` gathers the
-        resident shard's window inside the kernels."""
+        resident shard's window inside the kernels; ``/local`` variants skip the cross-GPU reduction."""
+        key = key or mode
         self._windowed = mode == "window"
         self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
         snap = [t.clone() for t in (self.flat_params, self.shadow, self.dev_step, *self.slots)]
         if self.p2p is not None:
             self.p2p.barrier()
-        self._step_body()
+        self._step_body(peers)
         torch.cuda.synchronize()
         if self.p2p is not None:
             self.p2p.barrier()
@@ -738,16 +943,61 @@ class NativeEngine:
             t.copy_(s)
         torch.cuda.synchronize()
         self._mail[self.opt_step % self._MAIL_RING] = 0        # the rolled-back warm-up step mailed a loss too
+        self._aux[self.opt_step % self._MAIL_RING] = 0
         if self.p2p is not None:
             self.p2p.barrier()
         g = torch.cuda.CUDAGraph()
         launches = N.LAUNCHES
         with torch.cuda.graph(g, stream=self._side):
-            self._step_body()
+            self._step_body(peers)
         self.launches_per_step = N.LAUNCHES - launches
-        self._graphs[mode] = g
+        self._graphs[key] = g
         self._graph = g
         torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ parameter averaging (mpipy.py:95-153)
+    def average_params(self, ranges, root_only: bool = False, include_momentum: bool = False) -> None:
+        """COLLECTIVE.  The reference's ``bcast_parameters`` as ONE kind of kernel over peer memory: the element
+        ranges ``[(offset, numel), ...]`` of the fp32 parameters (optionally of the optimizer slots too) are replaced
+        by their mean over ranks, in place, on every rank - or on rank 0 only with ``root_only`` (the literal
+        ``mpipy.py:129`` behaviour).  No host staging, no extra copy, no synchronize: K1 in plain-allreduce mode with
+        grads := params.  Owner-sliced algorithms only: rank r is the sole reader of slice r on every peer and its
+        sole writer afterwards, which is what makes in-place safe; the bf16 shadow is rewritten in the same pass."""
+        if self.p2p is None or self.world == 1:
+            return
+        bufs = [(self._param_ptrs, self._param_mc, True)]
+        if include_momentum:
+            if not self._slot_ptrs and self.slots:
+                raise RuntimeError("optimizer slots are not peer-mapped: construct the engine with "
+                                   "sync='weight_avg' and sync_include_momentum=True")
+            bufs += [(ptrs, mc, False) for ptrs, mc in zip(self._slot_ptrs, self._slot_mc)]
+        merged = []
+        for off, numel in sorted(ranges):
+            lo, hi = off // 4 * 4, min(self.n, (off + numel + 3) // 4 * 4)     # padding between tensors is zero everywhere
+            if merged and lo <= merged[-1][1]:
+                merged[-1][1] = max(merged[-1][1], hi)
+            else:
+                merged.append([lo, hi])
+        for ptrs, mc, is_param in bufs:
+            for lo, hi in merged:
+                a = self.p2p.fused_args()
+                a.optimizer = -1
+                nvls = bool(mc) and self.world >= 4 and not root_only and self.cfg.comm_algo in ("auto", "nvls")
+                a.algo = 2 if nvls else 1
+                for r in range(self.world):
+                    a.grads[r] = a.params[r] = ptrs[r]
+                    if is_param and not self.fp32:
+                        a.shadow[r] = self._shadow_ptrs[r]
+                if nvls:
+                    a.mc_grads = a.mc_params = mc
+                    if is_param and not self.fp32 and self._shadow_mc:
+                        a.mc_shadow = self._shadow_mc
+                    elif is_param and not self.fp32:
+                        a.algo = 1
+                a.offset, a.count, a.scale = lo, hi - lo, 1.0 / self.world
+                a.dst_mask = 1 if root_only else 0
+                a.chan = 0
+                N.call("mtb_fused_allreduce_update", C.byref(a))
 
     # ------------------------------------------------------------------ inference
     def predict(self, x, dropout_step: Optional[int] = None) -> torch.Tensor:
@@ -762,21 +1012,58 @@ class NativeEngine:
         self._forward(B, dropout_step is not None, False)
         return self.probs[:B].clone()
 
+    def _eval_body(self, dev: torch.Tensor, out: torch.Tensor, B: int, dropout: bool):
+        """The reference's ``eval_in_batches`` loop (``mpipy.py:174-182``) as a sequence of kernel launches that read
+        the resident split in place and write the probabilities straight into ``out``."""
+        size = dev.shape[0]
+        self._windowed, self._stream_buf = False, None
+        keep_x, keep_probs = self.x_in, self.probs
+        try:
+            for begin in range(0, size, B):
+                if begin + B <= size:
+                    self.x_in, self.probs = dev[begin:begin + B], out[begin:begin + B]
+                    self._forward(B, dropout, False)
+                else:                                   # ragged tail: the last B rows again, keep the needed suffix
+                    self.x_in, self.probs = dev[size - B:], keep_probs
+                    self._forward(B, dropout, False)
+                    out[begin:].copy_(keep_probs[begin - size + B:B])
+        finally:
+            self.x_in, self.probs = keep_x, keep_probs
+
     def predict_all(self, data, B: int, dropout_step: Optional[int] = None) -> np.ndarray:
-        """``eval_in_batches`` (``mpipy.py:169-183``) with the data uploaded once."""
+        """``eval_in_batches`` (``mpipy.py:169-183``).  The split is uploaded ONCE and stays resident (the reference
+        re-feeds it every step: ~157 host->device feeds per evaluation at N=1, ``mpipy.py:86,177``); the whole loop
+        over it is captured in one CUDA graph per (split, batch, dropout) and replayed, so an evaluation is one
+        launch plus one device->host copy of the probabilities.  Dropout at eval (the reference's behaviour,
+        ``mpipy.py:166`` via ``:68``) uses the device step counter's stream, as training does."""
         if isinstance(data, np.ndarray):
             data = torch.from_numpy(data)
         size = data.shape[0]
-        dev = data.reshape(size, -1).to(self.device, dtype=torch.float32)
-        out = torch.empty(size, self.spec.num_classes, device=self.device)
-        for begin in range(0, size, B):
-            end = begin + B
-            if end <= size:
-                out[begin:end] = self.predict(dev[begin:end], dropout_step)
-            else:
-                out[begin:] = self.predict(dev[-B:], dropout_step)[begin - size:]
-        return out.cpu().numpy()
+        if B > self.Bmax:
+            raise ValueError(f"batch {B} exceeds the engine's static capacity {self.Bmax}")
+        key = (data.data_ptr(), tuple(data.shape), B, dropout_step is not None)
+        ent = self._eval_cache.get(key)
+        if ent is None:
+            if len(self._eval_cache) >= 8:
+                self._eval_cache.clear()
+            dev = data.reshape(size, -1).to(self.device, dtype=torch.float32).contiguous()
+            out = torch.empty(size, self.spec.num_classes, device=self.device)
+            ent = {"dev": dev, "out": out, "graph": None, "host": data}      # `host` pins the key's address
+            self._eval_cache[key] = ent
+            if self.cfg.cuda_graph:
+                self._eval_body(dev, out, B, dropout_step is not None)      # warm-up: attributes, tensor maps
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self._side):
+                    self._eval_body(dev, out, B, dropout_step is not None)
+                ent["graph"] = g
+        if ent["graph"] is not None:
+            ent["graph"].replay()
+        else:
+            self._eval_body(ent["dev"], ent["out"], B, dropout_step is not None)
+        return ent["out"].cpu().numpy()
 
     def close(self):
         self._graph = None
         self._graphs = {}
+        self._eval_cache = {}

@@ -35,6 +35,12 @@ class FusedArgs(C.Structure):
         ("advance_step", vp), ("done_counter", vp),
         ("loss_src", vp), ("loss_mail", vp), ("loss_ring", i32),
         ("n_prered", i32), ("prered_begin", i64 * 2), ("prered_end", i64 * 2),
+        ("chan", i32),
+        ("push_recv", vp * 16), ("push_stride", i64),
+        ("grads_lp", vp * 16), ("mc_grads_lp", vp), ("lp_begin", i64), ("lp_end", i64),
+        ("dst_mask", C.c_uint),
+        ("l2_blocks", vp), ("l2_slots", vp * 16), ("l2_row", i32), ("l2_rows_n", i32 * 4),
+        ("err_src", vp), ("aux_mail", vp),
     ]
 
 

@@ -75,9 +75,10 @@ class P2PComm(Communicator):
         self.has_multicast = False
         self._allocs: List[Tuple[int, List[int]]] = []
         flag_bytes = self._L.mtb_fused_flag_bytes()
-        # control block: [flags | seq (1 KiB) | status (256 B)]
+        # control block: [flags | seq (2 KiB) | status (256 B) | tagged L2 partial slots (4 rows x 16 ranks x 8 B)]
         self._seq_bytes = 4 * self._L.mtb_fused_max_blocks()
-        self.ctrl = self.alloc_symmetric(flag_bytes + self._seq_bytes + 256)
+        self._l2_off = flag_bytes + self._seq_bytes + 256
+        self.ctrl = self.alloc_symmetric(self._l2_off + 4 * 16 * 8)
         self._flag_bytes = flag_bytes
         self.staging = self.alloc_symmetric(staging_bytes)
         self.staging_bytes = staging_bytes
@@ -122,6 +123,7 @@ class P2PComm(Communicator):
         a.world, a.rank = self.size, self.rank
         for r in range(self.size):
             a.flags[r] = self.ctrl.ptrs[r]
+            a.l2_slots[r] = self.ctrl.ptrs[r] + self._l2_off
         a.seq = self.ctrl.local_ptr + self._flag_bytes
         a.status = self.ctrl.local_ptr + self._flag_bytes + self._seq_bytes
         a.lr_override = -1.0
@@ -159,7 +161,15 @@ class P2PComm(Communicator):
     def _is_dev(self, t: Optional[torch.Tensor]) -> bool:
         return t is not None and t.is_cuda
 
-    def allreduce(self, t: torch.Tensor, average: bool = False, algo: int = 0) -> None:
+    def _auto_algo(self, nbytes: int) -> int:
+        """One-shot below 256 KB (one flag round less), else the owner-sliced forms: the in-switch reduction from 4
+        GPUs up when the staging buffer has a multicast mapping, the plain two-shot otherwise (measured crossovers,
+        bench/allreduce_sweep.py)."""
+        if nbytes <= (256 << 10):
+            return 0
+        return 2 if (self.staging.mc_ptr and self.size >= 4 and nbytes <= (512 << 20)) else 1
+
+    def allreduce(self, t: torch.Tensor, average: bool = False, algo: Optional[int] = None) -> None:
         if not t.is_cuda:
             return self.boot.allreduce(t, average) if self.size > 1 else None
         if self.size == 1:
@@ -178,17 +188,29 @@ class P2PComm(Communicator):
             stage[:n].copy_(flat[off:off + n])
             if n4 > n:
                 stage[n:n4].zero_()
-            out = flat[off:off + n] if n4 == n else torch.empty(n4, dtype=torch.float32, device=t.device)
+            use = self._auto_algo(n4 * 4) if algo is None else algo
             a = self.fused_args()
-            a.algo, a.optimizer = 0, -1
+            a.algo, a.optimizer = use, -1
             for r in range(self.size):
                 a.grads[r] = self.staging.ptrs[r]
-            a.params[self.rank] = out.data_ptr()
             a.offset, a.count = 0, n4
             a.scale = (1.0 / self.size) if average else 1.0
-            N.call("mtb_fused_allreduce_update", C.byref(a))
-            if n4 != n:
-                flat[off:off + n].copy_(out[:n])
+            if use == 0:
+                # every rank reduces the whole message: the result goes straight to the caller's tensor
+                out = flat[off:off + n] if n4 == n else torch.empty(n4, dtype=torch.float32, device=t.device)
+                a.params[self.rank] = out.data_ptr()
+                N.call("mtb_fused_allreduce_update", C.byref(a))
+                if n4 != n:
+                    flat[off:off + n].copy_(out[:n])
+            else:
+                # owner-sliced, in place on the staging buffer: rank r is the only reader of slice r on every peer and
+                # the only writer of it afterwards, and the kernel's closing flag round covers the peer stores
+                for r in range(self.size):
+                    a.params[r] = self.staging.ptrs[r]
+                if use == 2:
+                    a.mc_grads = a.mc_params = self.staging.mc_ptr
+                N.call("mtb_fused_allreduce_update", C.byref(a))
+                flat[off:off + n].copy_(stage[:n])
         torch.cuda.current_stream().synchronize()
         self.check_status()
 

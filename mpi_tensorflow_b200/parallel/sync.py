@@ -43,7 +43,7 @@ class GradAllreduce:
             self.comm.allreduce(flat_grads, average=True)
 
     def after_step(self, step: int, flat_params: torch.Tensor,
-                   flat_slots: Optional[List[torch.Tensor]] = None) -> bool:
+                   flat_slots: Optional[List[torch.Tensor]] = None, engine=None) -> bool:
         return False
 
 
@@ -63,8 +63,15 @@ class WeightAverage:
         return step > 0 and step % self.period == 0          # mpipy.py:87
 
     def after_step(self, step: int, flat_params: torch.Tensor,
-                   flat_slots: Optional[List[torch.Tensor]] = None) -> bool:
+                   flat_slots: Optional[List[torch.Tensor]] = None, engine=None) -> bool:
+        """Returns True when ``flat_params`` was rewritten by this call from OUTSIDE the engine (the caller then
+        refreshes derived copies).  With a GPU engine on the peer-memory backend the averaging is one fused kernel
+        over NVLink that also rewrites the bf16 shadow (``NativeEngine.average_params``): nothing left to refresh."""
         if not self.due(step) or self.comm.size == 1:
+            return False
+        if engine is not None and hasattr(engine, "average_params") and getattr(self.comm, "backend", "") == "p2p":
+            engine.average_params(_ranges(self.spec, self.include_bias), root_only=self.root_only,
+                                  include_momentum=self.include_momentum)
             return False
         bufs = [flat_params] + (list(flat_slots or []) if self.include_momentum else [])
         for buf in bufs:
@@ -96,7 +103,7 @@ class NoSync:
     def reduce_grads(self, flat_grads):
         pass
 
-    def after_step(self, step, flat_params, flat_slots=None):
+    def after_step(self, step, flat_params, flat_slots=None, engine=None):
         return False
 
 

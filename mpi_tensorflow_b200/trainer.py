@@ -55,13 +55,17 @@ class Trainer:
         self.engine = engine or make_engine(cfg, self.comm, device)
         self.sync = make_sync(cfg, self.comm, self.spec)
         self.log = RunLogger(self.comm.rank, self.comm.size, cfg.log_jsonl, cfg.log_all_ranks)
-        self.timer = PhaseTimer(device.type == "cuda")
+        self.timer = PhaseTimer(device.type == "cuda", enabled=cfg.profile_phases)
         self.global_step = 0
         self.shards: Optional[D.Shards] = None
         self.sampler = None
         self.decay_rows = cfg.lr_decay_rows
         self._fault = FaultSpec.from_env()
-        self._fused = getattr(self.engine, "can_fuse", False) and cfg.sync in ("grad_allreduce", "none")
+        # The GPU engine runs every strategy through its fused, graph-captured step: with the per-step gradient
+        # allreduce inside K1 (sync="grad_allreduce"), or as LOCAL steps (sync="weight_avg" between two averagings,
+        # sync="none") - the cross-GPU reduction happens only when the strategy asks for it.
+        self._fused = getattr(self.engine, "can_fuse", False)
+        self._peers = cfg.sync == "grad_allreduce"
         if cfg.resume:
             self.load_checkpoint(cfg.resume)
 
@@ -131,7 +135,11 @@ class Trainer:
                 idx = self.sampler.indices(step)
                 images, labels = self.shards.train_x[idx], self.shards.train_y[idx]
         if self._fused:
-            loss = self.engine.fused_step(images, labels, lr, step, read_loss=read_loss)
+            with self.timer.phase("step"):
+                loss = self.engine.fused_step(images, labels, lr, step, read_loss=read_loss, peers=self._peers)
+            if not self._peers:
+                with self.timer.phase("weight_sync"):
+                    self.sync.after_step(step, self.engine.flat_params, self.engine.slots, engine=self.engine)
         else:
             with self.timer.phase("fwd_bwd"):
                 loss = self.engine.compute_grads(images, labels, step)
@@ -154,11 +162,11 @@ class Trainer:
         already.  Returns the list of per-step losses."""
         x = torch.as_tensor(images, dtype=torch.float32)
         y = torch.as_tensor(labels).to(torch.int32)
-        if not self._fused or not hasattr(self.engine, "stream_steps"):
+        if not self._fused or not hasattr(self.engine, "stream_steps") or self.cfg.sync == "weight_avg":
             B, rows = self.cfg.batch, x.shape[0]
             out = []
             for i in range(steps):
-                o = (i % (rows // B)) * B
+                o = (self.global_step * B) % (rows - B) if rows > B else 0       # mpipy.py:80-82, global step
                 out.append(self.step(x[o:o + B], y[o:o + B]))
             return out
         x = x if x.is_pinned() else x.pin_memory()
@@ -166,7 +174,7 @@ class Trainer:
         if not self.decay_rows:
             self.decay_rows = x.shape[0]
             self.engine.decay_rows = self.engine.decay_rows or x.shape[0]
-        losses = self.engine.stream_steps(x, y, steps)
+        losses = self.engine.stream_steps(x, y, steps, peers=self._peers)
         self.global_step += steps
         return losses
 
@@ -216,21 +224,38 @@ class Trainer:
         t0 = time.time()
         last_loss, test_err = float("nan"), float("nan")
         imgs_at_log, t_at_log = 0, t0
+        phases = {}
         try:
             while self.global_step < steps:
                 step = self.global_step
-                last_loss = self.step()
+                log_now = bool(c.log_every) and step > 0 and step % c.log_every == 0
+                if log_now and c.profile_phases and self._fused and hasattr(self.engine, "timed_step"):
+                    # this step runs eagerly with events between its phases (every rank takes the same branch)
+                    phases = self.engine.timed_step(peers=self._peers)
+                    last_loss = self.engine._await_loss(self.engine.opt_step)
+                    if not self._peers:
+                        self.sync.after_step(step, self.engine.flat_params, self.engine.slots, engine=self.engine)
+                    self.global_step += 1
+                else:
+                    last_loss = self.step()
                 if wd:
                     wd.kick()
                 if c.eval_every and (step % c.eval_every == 0) and (c.eval_every == 1 or step > 0):
                     test_err = self.evaluate("test")
-                if c.log_every and step > 0 and step % c.log_every == 0:                   # mpipy.py:87
+                if log_now:                                                                # mpipy.py:87
                     self.engine.synchronize()
                     now = time.time()
                     ips = (step * c.batch - imgs_at_log) / max(1e-9, now - t_at_log)
                     imgs_at_log, t_at_log = step * c.batch, now
-                    self.log.log(step=step, loss=last_loss, lr=self.lr_at(step), test_error=test_err,
-                                 img_per_s=ips * self.comm.size)
+                    rec = dict(step=step, loss=last_loss, lr=self.lr_at(step), test_error=test_err,
+                               img_per_s=ips * self.comm.size)
+                    if hasattr(self.engine, "train_errors") and self._fused:               # mpipy.py:89, kept
+                        rec["train_error"] = 100.0 * self.engine.train_errors(self.engine.opt_step) / c.batch
+                    if phases:
+                        rec.update(fwd_us=phases["fwd"], bwd_us=phases.get("bwd", 0.0) + phases.get("bwd_fc", 0.0)
+                                   + phases.get("bwd_conv", 0.0), allreduce_us=phases["k1_hidden"] + phases["k1_tail"],
+                                   allreduce_exposed_us=phases["k1_tail"], bus_gbs=phases["bus_gbs"])
+                    self.log.log(**rec)
                 if c.checkpoint_dir and c.checkpoint_every and step > 0 and step % c.checkpoint_every == 0:
                     self.save_checkpoint(os.path.join(c.checkpoint_dir, f"model.ckpt-{step}"))
         except CommError:

@@ -15,7 +15,11 @@ import torch
 
 
 class PhaseTimer:
-    def __init__(self, cuda: bool):
+    """``enabled=False`` (the default of the training loop) makes :meth:`phase` free: no events are created and
+    nothing accumulates, so a long run does not pay for timing nobody reads (``TrainConfig.profile_phases``)."""
+
+    def __init__(self, cuda: bool, enabled: bool = True):
+        self.enabled = enabled
         self.cuda = cuda and torch.cuda.is_available()
         self._pending: Dict[str, List] = defaultdict(list)
         self.totals_ms: Dict[str, float] = defaultdict(float)
@@ -23,6 +27,9 @@ class PhaseTimer:
 
     @contextlib.contextmanager
     def phase(self, name: str):
+        if not self.enabled:
+            yield
+            return
         if self.cuda:
             torch.cuda.nvtx.range_push(name)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

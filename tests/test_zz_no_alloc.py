@@ -75,14 +75,63 @@ def test_noalloc_splitk_matches_regular_entry_point(M, N, K, a_mn, b_mn, bn, spl
     assert float((ref - expect).norm() / expect.norm()) < 1e-4
 
     assert ws.numel() <= L.mtb_gemm_noalloc_max_workspace_bytes()
+    outs = [torch.full((M, N), float("nan"), device=dev) for _ in range(2)]
+    # the first call on a device resolves the scratch array's address (documented start-up step; the CUDA runtime
+    # may load the kernel image lazily at that point, which is the driver's business, not an allocation of ours)
+    rc = L.mtb_gemm_bf16_splitk_noalloc(A_st.data_ptr(), B_st.data_ptr(), outs[0].data_ptr(), M, N, K, int(a_mn),
+                                        int(b_mn), lda, ldb, N, 0, bias_p, int(relu), bn, splits, stream)
+    assert rc == 0, L.mtb_last_error()
+    outs[0].fill_(float("nan"))
+    torch.cuda.synchronize()
+    # "allocates nothing" is checked, not assumed: neither the driver's free-memory figure nor the tensor
+    # library's own books may move across the two calls (the outputs were allocated above, by the caller)
+    free0, _ = torch.cuda.mem_get_info(dev)
+    torch_alloc0, torch_res0 = torch.cuda.memory_allocated(dev), torch.cuda.memory_reserved(dev)
     for call in range(2):                         # the second call starts from the first one's leftovers
-        out = torch.full((M, N), float("nan"), device=dev)
+        out = outs[call]
         rc = L.mtb_gemm_bf16_splitk_noalloc(A_st.data_ptr(), B_st.data_ptr(), out.data_ptr(), M, N, K, int(a_mn),
                                             int(b_mn), lda, ldb, N, 0, bias_p, int(relu), bn, splits, stream)
         assert rc == 0, L.mtb_last_error()
-        torch.cuda.synchronize()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(dev)
+    assert free1 == free0, f"device memory moved by {free0 - free1} bytes across the allocation-free calls"
+    assert (torch.cuda.memory_allocated(dev), torch.cuda.memory_reserved(dev)) == (torch_alloc0, torch_res0)
+    for call, out in enumerate(outs):
         assert torch.isfinite(out).all(), f"call {call}"
         assert float((out - ref).norm() / ref.norm()) < 1e-5, f"call {call}"
+
+
+def test_noalloc_rejects_unsupported_tile_width():
+    """bn = 256 exists in the regular entry point only; here it is an argument error, not a silent change of tile."""
+    L = _lib()
+    dev = torch.device("cuda", 0)
+    A = torch.zeros(128, 128, dtype=torch.bfloat16, device=dev)
+    B = torch.zeros(128, 128, dtype=torch.bfloat16, device=dev)
+    out = torch.zeros(128, 128, device=dev)
+    rc = L.mtb_gemm_bf16_splitk_noalloc(A.data_ptr(), B.data_ptr(), out.data_ptr(), 128, 128, 128, 0, 0, 128, 128, 128,
+                                        0, None, 0, 256, 2, torch.cuda.current_stream().cuda_stream)
+    assert rc == 2                                # MTB_E_ARG
+    assert b"bn" in L.mtb_last_error()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs a second GPU")
+def test_noalloc_on_a_second_device():
+    """Every GPU that loads the library has its own copy of the array and its own kernel attributes."""
+    L = _lib()
+    dev = torch.device("cuda", 1)
+    with torch.cuda.device(dev):
+        M, N, K = 256, 128, 1024
+        g = torch.Generator(device="cpu").manual_seed(7)
+        A = torch.randn(M, K, generator=g).to(torch.bfloat16).to(dev)
+        B = torch.randn(N, K, generator=g).to(torch.bfloat16).to(dev)
+        out = torch.zeros(M, N, device=dev)
+        for _ in range(2):
+            rc = L.mtb_gemm_bf16_splitk_noalloc(A.data_ptr(), B.data_ptr(), out.data_ptr(), M, N, K, 0, 0, K, K, N, 0,
+                                                None, 0, 64, 4, torch.cuda.current_stream(dev).cuda_stream)
+            assert rc == 0, L.mtb_last_error()
+        torch.cuda.synchronize(dev)
+        expect = A.float() @ B.float().t()
+        assert float((out - expect).norm() / expect.norm()) < 1e-4
 
 
 def test_noalloc_refuses_shapes_beyond_the_builtin_scratch():
