@@ -164,30 +164,18 @@ __device__ __forceinline__ void rs_store_staged(const GemmParams& p, const float
 }
 #endif
 
-// CM x CN thread-block clusters: the CN CTAs of a cluster row work on the same M tile and each
-// loads 1/CN of the A tile, multicast to all of them; the CM CTAs of a cluster column share the
-// B tile the same way.  L2 -> SM traffic per CTA drops from A+B to A/CN + B/CM, which is what
-// bounds these GEMMs (tiles are small because the batch is).
 // TF32 = true: fp32 operands in shared memory, kind::tf32 MMAs (K = 8 per instruction).  A 128-byte swizzle row
 // then holds 32 elements instead of 64, so a stage covers 32 K and an MN-major atom is 32 elements wide; the
 // byte geometry (16 KB of A per stage, 32 bytes of K per MMA in K-major form) is the same as for bf16.
-template <int BN, bool A_MN, bool B_MN, int CM, int CN, bool TF32 = false>
+template <int BN, bool A_MN, bool B_MN, bool TF32 = false>
 __global__ void __launch_bounds__(kThreads, TF32 ? 2 : 1)      // fp32 path: two CTAs per SM when the smem ring is short
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const GemmParams p) {
   using C = Cfg<BN>;
   const int S = TF32 ? p.stages : C::kStages;        // compile-time for the bf16 instantiations
-  constexpr bool kCluster = CM * CN > 1;
-  static_assert(!(TF32 && kCluster), "the multicast variants are bf16 only");
   constexpr int kBKe = TF32 ? 32 : 64;             // K elements per stage (one 128-byte row)
   constexpr int kBlkE = TF32 ? 32 : 64;            // MN elements per MN-major atom column
   constexpr int kBlkBytes = kBKe * 128;            // one MN-major block: kBKe K-rows of 128 bytes
-  const int cx = CM > 1 ? (int)(blockIdx.x % CM) : 0, cy = CN > 1 ? (int)(blockIdx.y % CN) : 0;
-  uint16_t row_mask = 0, col_mask = 0;            // cluster ranks (x + y*CM) that share my A / my B
-#pragma unroll
-  for (int j = 0; j < CN; ++j) row_mask |= (uint16_t)(1u << (cx + j * CM));
-#pragma unroll
-  for (int i = 0; i < CM; ++i) col_mask |= (uint16_t)(1u << (i + cy * CM));
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -206,8 +194,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
-    // a stage is reusable once every CTA that multicasts into it has seen it consumed
-    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CM + CN - 1); }
+    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
@@ -216,7 +203,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
-  if (kCluster) cluster_sync_all();                // peers' barriers exist before anything is multicast to them
   mtb::pdl_sync();
 
   if (warp == 0) {
@@ -228,39 +214,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         const int kc = (kb0 + i) * kBKe;
         uint8_t* a = sA + s * C::kABytes;
         uint8_t* b = sB + s * C::kBBytes;
-        if (CN == 1) {
-          if (!A_MN) {
-            tma_load_2d(a, &tma_a, &full_bar[s], kc, tile_m * BM);
-          } else {
-#pragma unroll
-            for (int h = 0; h < BM / kBlkE; ++h)
-              tma_load_2d(a + h * kBlkBytes, &tma_a, &full_bar[s], tile_m * BM + h * kBlkE, kc);
-          }
-        } else if (!A_MN) {                        // my BM/CN rows of the K-major tile, to the whole cluster row
-          constexpr int R = BM / CN;
-          tma_load_2d_mc(a + cy * R * 128, &tma_a, &full_bar[s], kc, tile_m * BM + cy * R, row_mask);
-        } else {                                   // my 64/CN K-rows of both 64-wide MN atoms
-          constexpr int R = 64 / CN;
-#pragma unroll
-          for (int h = 0; h < BM / 64; ++h)
-            tma_load_2d_mc(a + h * 8192 + cy * R * 128, &tma_a, &full_bar[s], tile_m * BM + h * 64, kc + cy * R, row_mask);
-        }
-        if (CM == 1) {
-          if (!B_MN) {
-            tma_load_2d(b, &tma_b, &full_bar[s], kc, tile_n * BN);
-          } else {
-#pragma unroll
-            for (int h = 0; h < BN / kBlkE; ++h)
-              tma_load_2d(b + h * kBlkBytes, &tma_b, &full_bar[s], tile_n * BN + h * kBlkE, kc);
-          }
-        } else if (!B_MN) {
-          constexpr int R = BN / CM;
-          tma_load_2d_mc(b + cx * R * 128, &tma_b, &full_bar[s], kc, tile_n * BN + cx * R, col_mask);
+        if (!A_MN) {
+          tma_load_2d(a, &tma_a, &full_bar[s], kc, tile_m * BM);
         } else {
-          constexpr int R = 64 / CM;
 #pragma unroll
-          for (int h = 0; h < BN / 64; ++h)
-            tma_load_2d_mc(b + h * 8192 + cx * R * 128, &tma_b, &full_bar[s], tile_n * BN + h * 64, kc + cx * R, col_mask);
+          for (int h = 0; h < BM / kBlkE; ++h)
+            tma_load_2d(a + h * kBlkBytes, &tma_a, &full_bar[s], tile_m * BM + h * kBlkE, kc);
+        }
+        if (!B_MN) {
+          tma_load_2d(b, &tma_b, &full_bar[s], kc, tile_n * BN);
+        } else {
+#pragma unroll
+          for (int h = 0; h < BN / kBlkE; ++h)
+            tma_load_2d(b + h * kBlkBytes, &tma_b, &full_bar[s], tile_n * BN + h * kBlkE, kc);
         }
       }
     }
@@ -296,9 +262,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
           for (int k = 1; k < BK / 16; ++k) mma_f16_acc(tmem_base, da + k * a_kstep, db + k * b_kstep, idesc);
         }
-        // smem slot reusable once these MMAs retire: tell every CTA that multicasts into it
-        if (kCluster) mma_commit_mc(&empty_bar[s], row_mask | col_mask);
-        else mma_commit(&empty_bar[s]);
+        mma_commit(&empty_bar[s]);       // smem slot reusable once these MMAs retire
         if (++s == S) { s = 0; ph ^= 1; }
       }
       mma_commit(tmem_full);             // accumulator complete
@@ -376,7 +340,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     tc_fence_before();
   }
   __syncthreads();
-  if (kCluster) cluster_sync_all();                // nobody leaves while a peer may still signal its barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<BN>(tmem_base);
@@ -410,9 +373,9 @@ bool get_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, u
   return true;
 }
 
-template <int BN, bool A_MN, bool B_MN, int CM = 1, int CN = 1, bool TF32 = false>
+template <int BN, bool A_MN, bool B_MN, bool TF32 = false>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CM, CN, TF32>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, TF32>;
   // the opt-in to more than 48 KB of dynamic shared memory is a per-device property of the function
   static bool attr_set[64] = {};
   int dev = 0;
@@ -426,7 +389,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
   q.stages = Cfg<BN>::kStages;
   if (TF32 && p.kb_per_split < q.stages) q.stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
   const size_t smem = 1024 + (size_t)q.stages * (Cfg<BN>::kABytes + Cfg<BN>::kBBytes) + 256;
-  MTB_CUDA_CHECK(mtb::launch_cluster(kern, grid, dim3(kThreads), smem, st, dim3(CM, CN, 1), ma, mb, q));
+  MTB_CUDA_CHECK(mtb::launch(kern, grid, dim3(kThreads), smem, st, ma, mb, q));
   return 0;
 }
 
@@ -512,37 +475,15 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   p.keep_prob = keep_prob; p.seed = seed; p.step_ptr = step_ptr;
   p.workspace = reinterpret_cast<float*>(workspace);
   p.counters = reinterpret_cast<unsigned int*>(counters);
-  // Cluster shape: share the operand whose tile dimension the grid divides evenly.  Instantiated for
-  // the three products of the FC layers: fprop (BN 64, A K-major, B MN-major) and wgrad (BN 128,
-  // both MN-major) share A across 4 or 2 CTAs along N; dgrad (BN 128, both K-major) shares B along M.
-  const int tiles_m = (int)mtb::ceil_div(M, BM), tiles_n = (int)mtb::ceil_div(N, bn);
-  int cm = 1, cn = 1;
-  // Measured on the FC shapes (scripts/bench_gemm.py): multicast brings nothing (13.5 vs 13.4 us fprop, dgrad and
-  // wgrad 2 us slower) because these GEMMs are not L2-bound, so it is opt-in: MTB_GEMM_CLUSTER=1.
-  static const bool use_clusters = []() { const char* e = getenv("MTB_GEMM_CLUSTER"); return e && e[0] == '1'; }();
-  if (use_clusters && tiles_m * tiles_n >= 16) {
-    const bool fprop_like = bn == 64 && !a_mn_major && b_mn_major;
-    const bool wgrad_like = bn == 128 && a_mn_major && b_mn_major;
-    const bool dgrad_like = bn == 128 && !a_mn_major && !b_mn_major;
-    if (fprop_like || wgrad_like) cn = tiles_n % 4 == 0 ? 4 : (tiles_n % 2 == 0 ? 2 : 1);
-    else if (dgrad_like) cm = tiles_m % 4 == 0 ? 4 : (tiles_m % 2 == 0 ? 2 : 1);
-  }
   CUtensorMap ma, mb;
   bool ok;
-  // K-major operand stored [MN rows, K cols]; MN-major operand stored [K rows, MN cols].  In a cluster each
-  // CTA loads a 1/cn (A) or 1/cm (B) slice of the tile: fewer rows per box.
-  ok = a_mn_major ? get_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, 64 / cn, 64)
-                  : get_map(&ma, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, BM / cn, 64);
+  // K-major operand stored [MN rows, K cols]; MN-major operand stored [K rows, MN cols].
+  ok = a_mn_major ? get_map(&ma, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, 64, 64)
+                  : get_map(&ma, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, BM, 64);
   MTB_REQUIRE(ok, "gemm: cuTensorMapEncodeTiled failed for A");
-  ok = b_mn_major ? get_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64 / cm, 64)
-                  : get_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, (uint32_t)bn / cm, 64);
+  ok = b_mn_major ? get_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64, 64)
+                  : get_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, (uint32_t)bn, 64);
   MTB_REQUIRE(ok, "gemm: cuTensorMapEncodeTiled failed for B");
-  if (cn == 4 && bn == 64) return launch<64, false, true, 1, 4>(ma, mb, p, stream);
-  if (cn == 2 && bn == 64) return launch<64, false, true, 1, 2>(ma, mb, p, stream);
-  if (cn == 4 && bn == 128) return launch<128, true, true, 1, 4>(ma, mb, p, stream);
-  if (cn == 2 && bn == 128) return launch<128, true, true, 1, 2>(ma, mb, p, stream);
-  if (cm == 4) return launch<128, false, false, 4, 1>(ma, mb, p, stream);
-  if (cm == 2) return launch<128, false, false, 2, 1>(ma, mb, p, stream);
 #define MTB_GEMM_CASE(BN_, AM_, BM_)                                            \
   if (bn == BN_ && (a_mn_major != 0) == AM_ && (b_mn_major != 0) == BM_) return launch<BN_, AM_, BM_>(ma, mb, p, stream);
   MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)
@@ -589,7 +530,7 @@ int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int 
   MTB_REQUIRE(ok, "gemm_tf32: cuTensorMapEncodeTiled failed for B");
 #define MTB_GEMM_CASE(BN_, AM_, BM_)                                            \
   if (bn == BN_ && (a_mn_major != 0) == AM_ && (b_mn_major != 0) == BM_)        \
-    return launch<BN_, AM_, BM_, 1, 1, true>(ma, mb, p, stream);
+    return launch<BN_, AM_, BM_, true>(ma, mb, p, stream);
   MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)
   MTB_GEMM_CASE(128, true, true) MTB_GEMM_CASE(64, false, false) MTB_GEMM_CASE(64, false, true)
   MTB_GEMM_CASE(64, true, false) MTB_GEMM_CASE(64, true, true)
