@@ -56,8 +56,9 @@ def parse():
     ap.add_argument("--comm-algo", default="auto")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--overlap", action="store_true", help="fc-bucket K1 on a comm stream under the conv backward")
-    ap.add_argument("--no-overlap", action="store_true", help="(default) one K1 launch at the end of the step")
+    ap.add_argument("--overlap", action="store_true", help="(default with peers) bucketed K1: fc bucket hidden under the conv backward")
+    ap.add_argument("--no-overlap", action="store_true", help="one whole-buffer K1 launch at the end of the step")
+    ap.add_argument("--comm-dtype", default="fp32", choices=["fp32", "bf16"], help="gradient wire format")
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--fuse-wgrad-rs", action="store_true",
                     help="FC1 weight gradient: GEMM -> reduce-scatter in one kernel over peer memory (N > 1)")
@@ -174,7 +175,7 @@ def run_ours(args) -> dict:
     B, K, W = args.batch, args.steps, args.warmup
     cfg = TrainConfig(model=args.model, batch=B, dtype=args.dtype, optimizer=args.optimizer, eval_every=0,
                       log_every=0, dropout=True, cuda_graph=not args.no_graph, comm_algo=args.comm_algo,
-                      overlap=args.overlap and not args.no_overlap, fuse_wgrad_rs=args.fuse_wgrad_rs,
+                      overlap=not args.no_overlap, fuse_wgrad_rs=args.fuse_wgrad_rs, comm_dtype=args.comm_dtype,
                       lr=0.01 if args.optimizer != "adam" else 1e-4)
     tr = Trainer(cfg, comm)
     eng = tr.engine
@@ -234,8 +235,9 @@ def run_ours(args) -> dict:
         ms3 = timed_region(comm, loop3)
         e2e = {"value": n * B * K / (ms2 / 1e3), "unit": "images/s", "ms_per_step": ms2 / K,
                "api": "Trainer.fit_stream(host_images, host_labels, steps)",
-               "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 8,
-               "d2h_how": "the update kernel stores {step, loss} (8 B) into a pinned host ring; the host polls it",
+               "h2d_bytes_per_step": B * 784 * 4 + B * 4, "d2h_bytes_per_step": 16,
+               "d2h_how": "the update kernel stores {step, loss} and {step, error count} (8 B each) into pinned host "
+                          "rings; the host polls them",
                "losses_read": len(got["losses"]), "loss_last": got["losses"][-1],
                "sync_step_api": {"api": "Trainer.step(images, labels)", "value": n * B * K / (ms3 / 1e3),
                                  "ms_per_step": ms3 / K}}
@@ -248,6 +250,7 @@ def run_ours(args) -> dict:
         "config": {"model": f"mnist_cnn_{args.model}", "global_batch": n * B, "per_rank_batch": B, "seq_len": 784,
                    "parallelism": f"dp{n}", "optimizer": args.optimizer, "cuda_graph": cfg.cuda_graph,
                    "l2": "inputs larger than L2: 172 MB per-rank shard streamed sequentially, no flush",
+                   "comm_dtype": args.comm_dtype, "overlap": bool(getattr(eng, "_overlap", False)),
                    "comm": ("fused P2P allreduce+update kernel" if n > 1 else "fused update kernel")
                            + (" + FC1 wgrad GEMM with reduce-scatter epilogue" if getattr(eng, "_rs_mode", False) else ""),
                    "math": ("fp32 storage and accumulation, TF32 tensor-core operands (kind::tf32), fp32 CUDA cores for "

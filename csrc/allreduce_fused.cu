@@ -49,7 +49,9 @@ using namespace mtb;
 constexpr int kMaxRanks = 16;
 constexpr int kMaxBlocks = 512;
 constexpr int kMaxRanges = 8;
-constexpr int kChanBlocks = kMaxBlocks / 2;         // two channels of flag / sequence blocks (concurrent launches)
+constexpr int kChan1Base = 448;                     // flag / sequence blocks: channel 0 = [0, 448), channel 1 = [448, 511),
+constexpr int kChan1Blocks = 63;                    // block 511 = the stand-alone barrier (concurrent launches never share)
+constexpr int kMaxL2Blocks = 4096;                  // per-block L2 partials of one launch
 constexpr int kL2Rows = 4;                          // launches of one step that can contribute an L2 partial
 constexpr long long kSpinLimit = 30000000000ll;     // ~15 s at 2 GHz
 
@@ -98,6 +100,7 @@ struct FusedParams {
   unsigned long long* l2_slots[kMaxRanks];          // every rank's [kL2Rows][kMaxRanks] tagged {step+1 : f32} words
   int l2_row;
   int l2_rows_n[kL2Rows];                           // mailing launch: entries to add per row (0 unused, 1 local, world sliced)
+  int no_flags;                                     // the caller brackets this launch with barrier launches instead
   const int* err_src;                               // batch error count, mailed next to the loss
   unsigned long long* aux_mail;                     // pinned host ring of {u32 errors, u32 step} words
 };
@@ -365,10 +368,17 @@ fused_allreduce_update_kernel(const FusedParams p) {
   __shared__ float s_red[8];
   __shared__ int s_last;
   pdl_sync();
-  if (threadIdx.x == 0) s_seq = p.world > 1 ? p.seq[fb] : 0u;
+  if (threadIdx.x == 0) s_seq = (p.world > 1 && !p.no_flags) ? p.seq[fb] : 0u;
   __syncthreads();
   const uint32_t seq = s_seq;
   const long long step = p.step_ptr ? *p.step_ptr : 0;
+  // what the closing warp mails was final before this launch began: fetch it now, off the closing chain's critical path
+  float loss_in = 0.f;
+  int err_in = 0;
+  if (threadIdx.x == 0 && p.loss_mail != nullptr) {
+    loss_in = __ldcg(p.loss_src);
+    if (p.err_src != nullptr) err_in = __ldcg(p.err_src);
+  }
   const Hyper h = make_hyper(p, step);
   const bool multi = p.world > 1;
   const bool sliced = multi && (p.algo == 1 || p.algo == 2);
@@ -388,7 +398,7 @@ fused_allreduce_update_kernel(const FusedParams p) {
   } else {
     // every peer's gradients are complete (with pre-reduced ranges some of them were written into MY memory by
     // peers' kernels: the fence makes this rank's own remote additions globally visible before it signals)
-    cross_gpu_barrier(p, fb, seq + 1, p.n_prered > 0);
+    if (!p.no_flags) cross_gpu_barrier(p, fb, seq + 1, p.n_prered > 0);
     if (p.algo == 0) {
       run_range<kOneShot>(p, h, 0, vec_total, l2);
     } else {
@@ -401,8 +411,10 @@ fused_allreduce_update_kernel(const FusedParams p) {
     }
     // peers are done reading my grads (loads have retired: their values were consumed) and, in the
     // two-shot / nvls forms, done writing my params (needs the fence)
-    cross_gpu_barrier(p, fb, seq + 2, p.algo != 0);
-    rounds = 2;
+    if (!p.no_flags) {
+      cross_gpu_barrier(p, fb, seq + 2, p.algo != 0);
+      rounds = 2;
+    }
   }
 
   const bool want_l2 = p.l2_blocks != nullptr;
@@ -417,7 +429,7 @@ fused_allreduce_update_kernel(const FusedParams p) {
     }
   }
   if (threadIdx.x == 0) {
-    if (multi) p.seq[fb] = seq + rounds;
+    if (multi && rounds) p.seq[fb] = seq + rounds;
     s_last = 0;
     if (p.done_counter != nullptr) {
       // every block read the step counter at its start; the last one to finish closes the launch
@@ -429,51 +441,61 @@ fused_allreduce_update_kernel(const FusedParams p) {
     }
   }
   __syncthreads();
-  if (!s_last || threadIdx.x != 0) return;
+  if (!s_last || threadIdx.x >= 32) return;
+  // The last block's first warp closes the launch.  Everything below is spread over its 32 lanes: a single thread
+  // walking hundreds of block partials (or 24 peer slots) pays one L2 round trip per element, tens of microseconds.
+  const int lane = threadIdx.x;
   __threadfence();
   const uint32_t tag = static_cast<uint32_t>(step + 1);
+  float total = 0.f;
   if (want_l2) {
-    float total = 0.f;
-    for (int k = 0; k < (int)gridDim.x; ++k) total += __ldcg(p.l2_blocks + k);      // block order: reproducible
+    float part = 0.f;
+    for (int k = lane; k < (int)gridDim.x; k += 32) part += __ldcg(p.l2_blocks + k);   // fixed order: reproducible
+    total = warp_sum(part);
     const unsigned long long word = tagged(tag, total);
     if (sliced) {                                    // I only walked my slice: every rank needs every partial
-      for (int r = 0; r < p.world; ++r)
-        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.l2_slots[r] + p.l2_row * kMaxRanks + p.rank), "l"(word)
-                     : "memory");
-    } else {
+      if (lane < p.world)
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.l2_slots[lane] + p.l2_row * kMaxRanks + p.rank),
+                     "l"(word) : "memory");
+    } else if (lane == 0) {
       asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.l2_slots[p.rank] + p.l2_row * kMaxRanks), "l"(word)
                    : "memory");
     }
   }
-  if (p.advance_step != nullptr) {
-    const long long next = step + 1;
-    *p.advance_step = next;
-    if (p.loss_mail != nullptr) {
-      float loss = *p.loss_src;
-      if (want_l2) {
-        // partials of this step, mine and the slice owners', in row / rank order; each word carries its step
-        float sum = 0.f;
-        const long long t0 = clock64();
-        for (int row = 0; row < kL2Rows; ++row)
-          for (int e = 0; e < p.l2_rows_n[row]; ++e) {
-            const unsigned long long* src = p.l2_slots[p.rank] + row * kMaxRanks + e;
-            unsigned long long w;
-            while (true) {
-              asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
-              if (static_cast<uint32_t>(w >> 32) == tag) break;
-              if (clock64() - t0 > kSpinLimit) { atomicExch(p.status, MTB_E_TIMEOUT); break; }
-            }
-            sum += __uint_as_float(static_cast<uint32_t>(w));
-          }
-        loss = fmaf(p.wd, sum, loss);
+  if (p.advance_step == nullptr) return;
+  const long long next = step + 1;
+  if (lane == 0) *p.advance_step = next;
+  if (p.loss_mail == nullptr) return;
+  float l2sum = 0.f;
+  if (want_l2) {
+    // partials of this step, mine and the slice owners'; each word carries its step, so a lane simply waits for its own
+    const long long t0 = clock64();
+#pragma unroll
+    for (int j = 0; j < (kL2Rows * kMaxRanks) / 32; ++j) {
+      const int e = lane + 32 * j, row = e / kMaxRanks, ent = e % kMaxRanks;
+      if (row == p.l2_row && !sliced) {
+        if (ent == 0) l2sum += total;                // my own complete partial: no need to read it back
+      } else if (ent < p.l2_rows_n[row]) {
+        const unsigned long long* src = p.l2_slots[p.rank] + e;
+        unsigned long long w;
+        while (true) {
+          asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+          if (static_cast<uint32_t>(w >> 32) == tag) break;
+          if (clock64() - t0 > kSpinLimit) { atomicExch(p.status, MTB_E_TIMEOUT); break; }
+        }
+        l2sum += __uint_as_float(static_cast<uint32_t>(w));
       }
-      // one 8-byte store = one PCIe write: the host sees the value and its step number together
-      const long long slot = (next - 1) & (p.loss_ring - 1);
-      if (p.aux_mail != nullptr && p.err_src != nullptr)
-        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.aux_mail + slot),
-                     "l"((static_cast<unsigned long long>(tag) << 32) | static_cast<uint32_t>(*p.err_src)) : "memory");
-      asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.loss_mail + slot), "l"(tagged(tag, loss)) : "memory");
     }
+    l2sum = warp_sum(l2sum);
+  }
+  if (lane == 0) {
+    const float loss = fmaf(p.wd, l2sum, loss_in);
+    // one 8-byte store = one PCIe write: the host sees the value and its step number together
+    const long long slot = (next - 1) & (p.loss_ring - 1);
+    if (p.aux_mail != nullptr && p.err_src != nullptr)
+      asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.aux_mail + slot),
+                   "l"((static_cast<unsigned long long>(tag) << 32) | static_cast<uint32_t>(err_in)) : "memory");
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.loss_mail + slot), "l"(tagged(tag, loss)) : "memory");
   }
 }
 
@@ -539,7 +561,9 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->loss_src = reinterpret_cast<const float*>(a->loss_src);
   p->loss_mail = reinterpret_cast<unsigned long long*>(a->loss_mail);
   p->loss_ring = a->loss_ring;
-  p->chan_base = a->chan * kChanBlocks;
+  p->chan_base = a->chan ? kChan1Base : 0;
+  p->no_flags = a->no_flags;
+  MTB_REQUIRE(!a->no_flags || a->algo != 3, "fused: push carries its own flag round");
   p->push_stride = a->push_stride;
   for (int r = 0; r < kMaxRanks; ++r) {
     p->push_recv[r] = reinterpret_cast<float*>(a->push_recv[r]);
@@ -593,15 +617,16 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   if (p.world > 1 && (p.algo == 1 || p.algo == 2)) vecs = (vecs + p.world - 1) / p.world;     // owner slices
   if (block < 32) block = 32;
   block = (block + 31) / 32 * 32;
-  // a lone GPU has no flag rounds to pay per block: cover the chip; with peers the blocks of one launch share a
-  // channel of 255 flag blocks
-  int grid = a->grid > 0 ? a->grid : (p.world == 1 ? 3 * 148 : kChanBlocks - 1);
   // one pass = 4 vectors (64 bytes) per thread; another block (and its flag round) pays off after that
   long long need = (vecs + 4 * block - 1) / (4 * block);
   if (need < 1) need = 1;
+  // grid < 0: one pass per block ("short-lived blocks": a launch that runs UNDER other kernels must not park blocks
+  // on an SM for its whole duration; leftover register space is handed back every few microseconds)
+  int grid = a->grid > 0 ? a->grid : (a->grid < 0 ? kMaxL2Blocks : 3 * 148);
   if (grid > need) grid = (int)need;
-  if (p.world > 1 && grid > kChanBlocks - 1) grid = kChanBlocks - 1;
-  if (grid > kMaxBlocks) grid = kMaxBlocks;
+  const bool flags = p.world > 1 && !p.no_flags;
+  if (flags && grid > (a->chan ? kChan1Blocks : kChan1Base)) grid = a->chan ? kChan1Blocks : kChan1Base;
+  if (grid > kMaxL2Blocks) grid = kMaxL2Blocks;
   MTB_CUDA_CHECK(mtb::launch(fused_allreduce_update_kernel, dim3(grid), dim3(block), 0, stream, p));
   return 0;
 }
@@ -623,6 +648,7 @@ int mtb_advance_step(long long* step_ptr, cudaStream_t stream) {
 }
 
 int mtb_fused_max_blocks(void) { return kMaxBlocks; }
+int mtb_fused_max_l2_blocks(void) { return kMaxL2Blocks; }
 int mtb_fused_flag_bytes(void) { return kMaxBlocks * kMaxRanks * (int)sizeof(uint32_t); }
 
 }  // extern "C"

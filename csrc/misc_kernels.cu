@@ -126,7 +126,33 @@ inline unsigned blocks_for(long long n, int threads) { return (unsigned)((n + th
 
 }  // namespace
 
+// Occupancy probe (scripts/, not the product): blocks that sit on the SMs for a given time without touching memory,
+// lean (a handful of registers) or fat (about 56 live registers per thread), to separate placement / register
+// co-residency effects from memory-system interference when a kernel runs under the persistent convolution kernels.
+template <bool FAT>
+__global__ void __launch_bounds__(256) occupy_kernel(long long cycles, float* sink) {
+  const long long t0 = clock64();
+  float acc[FAT ? 48 : 1];
+#pragma unroll
+  for (int i = 0; i < (FAT ? 48 : 1); ++i) acc[i] = (float)(threadIdx.x + i);
+  while (clock64() - t0 < cycles) {
+#pragma unroll
+    for (int i = 0; i < (FAT ? 48 : 1); ++i) acc[i] = fmaf(acc[i], 1.0001f, 0.5f);
+  }
+  float t = 0.f;
+#pragma unroll
+  for (int i = 0; i < (FAT ? 48 : 1); ++i) t += acc[i];
+  if (t == 12345.678f) *sink = t;
+}
+
 extern "C" {
+
+int mtb_debug_occupy(int grid, int block, int fat, long long cycles, float* sink, cudaStream_t stream) {
+  if (fat) occupy_kernel<true><<<grid, block, 0, stream>>>(cycles, sink);
+  else occupy_kernel<false><<<grid, block, 0, stream>>>(cycles, sink);
+  MTB_LAUNCH_CHECK();
+  return 0;
+}
 
 int mtb_init_trunc_normal(float* dst, long long n, float stddev, unsigned long long seed, unsigned stream_id,
                           cudaStream_t stream) {

@@ -140,6 +140,9 @@ int mtb_conv2_dgrad_unpool(const void* dflat_bf16, const void* pooled_bf16, cons
                            void* dx_bf16, int B, cudaStream_t stream);
 int mtb_conv2_wgrad_unpool(const void* x_bf16, const void* dflat_bf16, const void* pooled_bf16, const uint8_t* idx,
                            float* dW, float* db, void* workspace, int B, cudaStream_t stream);
+/* occupancy probe (scripts only): `grid` blocks of `block` threads that hold their SM slots for `cycles` clocks without
+ * memory traffic; fat = about 56 live registers per thread instead of a handful */
+int mtb_debug_occupy(int grid, int block, int fat, long long cycles, float* sink, cudaStream_t stream);
 /* probe of the shared-memory descriptor semantics the implicit-GEMM convolutions rely on (test only) */
 int mtb_debug_shift_mma(const void* A, const void* B, float* out, int mode, int row_bytes, int rows_total, int shift,
                         int base_off, cudaStream_t stream);
@@ -230,7 +233,10 @@ typedef struct mtb_fused_args {
   long long prered_begin[2], prered_end[2];
   /* Launches that may be in flight at the same time (a bucket on a communication stream under the rest of backward, the
    * closing bucket on the main stream) must use different channels: each has its own flag and sequence blocks. */
-  int chan;             /* 0 or 1 */
+  int chan;             /* 0 (up to 448 blocks) or 1 (up to 63 blocks) */
+  int no_flags;         /* 1: no flag rounds inside this launch; the caller runs mtb_p2p_barrier before it (peers' gradients
+                         * complete) and after it (peer loads and stores done) on the same stream.  Lets the launch use any
+                         * number of short-lived blocks (grid < 0: one pass per block). */
   /* algo 3, "push": one-shot for a small bucket with ONE flag round.  Every rank stores its gradients into its row of
    * each peer's receive area (rows double buffered by the parity of *step_ptr), signals, and reduces its local rows. */
   void* push_recv[16];  /* every rank's receive area, peer-mapped: [2][world][push_stride] floats */
@@ -257,6 +263,7 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
 int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */
 int mtb_advance_step(long long* step_ptr, cudaStream_t stream);             /* global_step=iter_, mpipy.py:66 */
 int mtb_fused_max_blocks(void);
+int mtb_fused_max_l2_blocks(void);      /* capacity needed for l2_blocks, in floats */
 int mtb_fused_flag_bytes(void);
 
 #ifdef __cplusplus

@@ -69,7 +69,9 @@ class NativeEngine:
                          and cfg.comm_algo not in ("oneshot", "push") and not self._lp)
         # bucketed overlap (default): the fc bucket's fused allreduce+update runs on the comm stream under the
         # convolution backward; the reduce-scatter GEMM needs the single whole-buffer launch instead
-        self._overlap = bool(cfg.overlap) and not self._rs_mode
+        # (on a lone GPU there is no flag round or NVLink latency to hide: one launch there unless MTB_OVERLAP_N1=1)
+        self._overlap = (bool(cfg.overlap) and not self._rs_mode
+                         and (self.world > 1 or os.environ.get("MTB_OVERLAP_N1") == "1"))
         self._rs_active = False                  # True only inside the fused step body
         self._rs_dirty = True                    # owners' fc1 slices must be zero when a fused step starts
         if self._rs_mode:
@@ -89,8 +91,11 @@ class NativeEngine:
         self.data_x = self.data_y = None
         self.rows = 0
         self.decay_rows = cfg.lr_decay_rows
-        self._side = torch.cuda.Stream(device=device)
-        self._comm_stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("MTB_COMM_PRIO", "-1")))
+        # The step's own kernels run (and are captured) at high priority and the hidden bucket's launches at normal
+        # priority: when SM resources free up the next convolution CTA is placed first and the update's blocks take
+        # what is left over.
+        self._side = torch.cuda.Stream(device=device, priority=-1)
+        self._comm_stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("MTB_COMM_PRIO", "0")))
         self._ev_fc, self._ev_c2, self._ev_done = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
         self._eval_cache: Dict = {}
         self._marks = None                       # list of (name, event) while a step is being phase-timed
@@ -144,7 +149,7 @@ class NativeEngine:
         self._push_stride = (self._tail_hi + 3) // 4 * 4
         self._push = self.p2p.alloc_symmetric(2 * self.world * self._push_stride * 4) if multi else None
         self._sliced: Dict = {}                  # (lo, hi) of every owner-sliced peer launch -> algo
-        self._l2_blocks = torch.zeros(2, 512, device=dev)
+        self._l2_blocks = torch.zeros(2, N.lib().mtb_fused_max_l2_blocks(), device=dev)
         self._l2_slots = torch.zeros(4 * 16, dtype=torch.int64, device=dev)          # world-1 stand-in for the p2p slots
         self.dev_step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.loss_acc = torch.zeros(1, device=dev)
@@ -608,7 +613,7 @@ class NativeEngine:
 
     def _update(self, peers: bool, lr_override: float = -1.0, lo: int = 0, hi: Optional[int] = None,
                 advance: bool = True, grid: int = 0, block: int = 0, chan: int = 0, l2_row: int = 0,
-                l2_rows=None, tail: bool = False):
+                l2_rows=None, tail: bool = False, no_flags: bool = False):
         """K1 over elements [lo, hi) of the flat buffers.  ``advance``: this launch closes the step (bumps the
         counter, mails loss + error count).  ``l2_row``: where its 0.5*sum(w^2) partial goes; ``l2_rows``: for the
         closing launch, {row: sliced?} of every launch of the step (its own included)."""
@@ -625,6 +630,7 @@ class NativeEngine:
             self._masters_dirty = self._masters_dirty or a.n_sharded > 0
             self._slots_dirty = True                                   # slots of non-owned slices are not maintained
         a.grid, a.block, a.chan = grid, block, chan
+        a.no_flags = int(no_flags and peers and a.algo != 3)
         if self._rs_active and sliced:
             fc1w = self.spec.param("fc1_weight")
             a.n_prered = 1
@@ -756,15 +762,30 @@ class NativeEngine:
         return out
 
     def _hidden_launch(self, peers: bool, lo: int, hi: int, row: int) -> bool:
-        """One bucket's fused allreduce+update on the comm stream: narrow blocks (128 threads, 64 registers) that fit
-        on an SM NEXT TO the persistent convolution-backward CTAs, a grid sized for the bytes, channel 0."""
+        """One bucket's fused allreduce+update on the comm stream, shaped to run UNDER the persistent convolution
+        kernels: many short-lived narrow blocks (64 threads, one 4-vector pass each) that fit into whatever registers
+        the resident convolution CTA leaves free and give them back every few microseconds, instead of blocks parked on
+        the SMs for the whole transfer.  That needs more blocks than there are flag slots, so the two flag rounds
+        are their own one-warp launches before and after the data launch."""
         multi = peers and self.p2p is not None and self.world > 1
-        grid = int(os.environ.get("MTB_K1_GRID_A", "96" if multi else "148"))
-        block = int(os.environ.get("MTB_K1_BLOCK_A", "128"))
+        grid = int(os.environ.get("MTB_K1_GRID_A", "-1"))
+        block = int(os.environ.get("MTB_K1_BLOCK_A", "64"))
+        probe = os.environ.get("MTB_K1_PROBE")              # "fat:60" / "lean:60": occupancy probe instead of K1 (scripts)
         with torch.cuda.stream(self._comm_stream):
+            if probe:
+                kind, us = probe.split(":")
+                N.call("mtb_debug_occupy", 148 if grid < 0 else grid, block, int(kind == "fat"),
+                       int(float(us) * 1900), self._status.data_ptr())
+                return None                                # no bucket was updated: the closing launch expects no L2 row
             if row == 0:
                 self._mark("k1_hidden_begin")
-            sliced = self._update(peers=peers, lo=lo, hi=hi, advance=False, grid=grid, block=block, chan=0, l2_row=row)
+            own_flags = os.environ.get("MTB_K1_INNER_FLAGS") == "1" or not multi
+            if not own_flags:
+                self.p2p.device_barrier()                  # every rank's gradients of this bucket are complete
+            sliced = self._update(peers=peers, lo=lo, hi=hi, advance=False, grid=grid, block=block, chan=0, l2_row=row,
+                                  no_flags=not own_flags)
+            if not own_flags:
+                self.p2p.device_barrier()                  # peers are done reading my gradients and writing my weights
             self._mark("k1_hidden_end")
         return sliced
 
@@ -810,7 +831,9 @@ class NativeEngine:
         self._mark("bwd_fc")
         self._ev_fc.record(main)
         comm.wait_event(self._ev_fc)
-        rows[0] = self._hidden_launch(peers, split, self.n, 0)
+        sliced = self._hidden_launch(peers, split, self.n, 0)
+        if sliced is not None:
+            rows[0] = sliced
         tail_hi = split
         hook = None
         big_conv2 = (split - c2) * 4 > int(os.environ.get("MTB_CONV2_BUCKET_BYTES", str(256 << 10)))
@@ -818,7 +841,9 @@ class NativeEngine:
             def hook():
                 self._ev_c2.record(main)
                 comm.wait_event(self._ev_c2)
-                rows[1] = self._hidden_launch(peers, c2, split, 1)
+                sliced = self._hidden_launch(peers, c2, split, 1)
+                if sliced is not None:
+                    rows[1] = sliced
             tail_hi = c2
         self._backward_conv(self.B, hook)
         self._mark("bwd_conv")

@@ -35,7 +35,7 @@ class FusedArgs(C.Structure):
         ("advance_step", vp), ("done_counter", vp),
         ("loss_src", vp), ("loss_mail", vp), ("loss_ring", i32),
         ("n_prered", i32), ("prered_begin", i64 * 2), ("prered_end", i64 * 2),
-        ("chan", i32),
+        ("chan", i32), ("no_flags", i32),
         ("push_recv", vp * 16), ("push_stride", i64),
         ("grads_lp", vp * 16), ("mc_grads_lp", vp), ("lp_begin", i64), ("lp_end", i64),
         ("dst_mask", C.c_uint),
@@ -103,6 +103,7 @@ _SIGS = {
     "mtb_fused_allreduce_update": [C.POINTER(FusedArgs), vp],
     "mtb_p2p_barrier": [C.POINTER(FusedArgs), vp],
     "mtb_advance_step": [vp, vp],
+    "mtb_debug_occupy": [i32, i32, i32, i64, vp],
     "mtb_debug_shift_mma": [vp, vp, vp, i32, i32, i32, i32, i32, vp],
     "mtb_debug_shift_mma32": [vp, vp, vp, i32, i32, i32, i32, vp],
     "mtb_conv2_fprop_pool": [vp, vp, vp, vp, vp, i32, vp],
@@ -140,6 +141,7 @@ def lib() -> C.CDLL:
     L.mtb_conv2_wgrad_workspace_bytes.argtypes = [i32]
     L.mtb_conv2_wgrad_workspace_bytes.restype = C.c_size_t
     L.mtb_fused_max_blocks.restype = i32
+    L.mtb_fused_max_l2_blocks.restype = i32
     L.mtb_fused_flag_bytes.restype = i32
     _LIB = L
     return L

@@ -76,6 +76,10 @@ class Trainer:
         c, comm = self.cfg, self.comm
         sizes = D.split_sizes(comm.size)
         if shards is None:
+            # Parsing or synthesising 60,000 images on rank 0 takes tens of seconds on a slow host; the others wait in
+            # the first scatter, so the per-step failure-detection timeout must not apply to this phase.
+            if hasattr(comm, "set_timeout"):
+                comm.set_timeout(max(600.0, float(c.step_timeout_s)))
             root = D.load_root_dataset(c.data, sizes, c.data_dir, c.seed, c.reference_split_bug) \
                 if comm.rank == 0 else None
             per = dict(train=sizes.train_rows_per_rank, test=sizes.test_rows_per_rank,
@@ -91,6 +95,8 @@ class Trainer:
                 out[split] = (rx.numpy(), ry.numpy())
             shards = D.Shards(out["train"][0], out["train"][1], out["test"][0], out["test"][1],
                               out["val"][0], out["val"][1])
+            if hasattr(comm, "set_timeout"):
+                comm.set_timeout(float(c.step_timeout_s))
         self.shards = shards
         rows = shards.train_x.shape[0]
         self.sampler = (D.SequentialSampler if c.sampler == "sequential" else D.ShuffleSampler)(rows, c.batch)

@@ -115,7 +115,8 @@ def test_fit_stream_matches_stepwise_training():
     a = Trainer(cfg, device=dev)
     la = a.fit_stream(x, y, 20)
     b = Trainer(cfg, device=dev)
-    lb = [b.step(x[(i % 8) * 64:(i % 8 + 1) * 64], y[(i % 8) * 64:(i % 8 + 1) * 64]) for i in range(20)]
+    win = [(i * 64) % (512 - 64) for i in range(20)]          # the reference's window on the global step, past one wrap
+    lb = [b.step(x[o:o + 64], y[o:o + 64]) for o in win]
     assert len(la) == 20 and a.global_step == 20
     # atomics reorder fp32 sums, so the two trajectories drift apart slowly: the first steps must
     # agree closely, later ones only in trend
@@ -130,11 +131,19 @@ def test_loss_mailbox_matches_device_accumulator():
     tr = Trainer(_cfg(batch=64), device=torch.device("cuda", 0))
     tr.load_data(_shards(256))
     eng = tr.engine
+    spec = get_spec("tutorial512")
+
+    def l2_now():
+        p = eng.get_params()
+        return sum(0.5 * float((p[q.key].astype(np.float64) ** 2).sum()) for q in spec.params if q.decay)
+
     for i in range(1, 20):                       # more steps than ring slots: slots are reused
+        l2 = l2_now()                            # the loss uses the weights BEFORE the update (mpipy.py:55-58)
         mailed = tr.step()
         torch.cuda.synchronize()
         assert eng.opt_step == i and int(eng.dev_step.item()) == i
-        assert mailed == pytest.approx(float(eng.loss_acc.item()), rel=0, abs=0)
+        assert mailed == pytest.approx(float(eng.loss_acc.item()) + 5e-4 * l2, rel=2e-6)
+        assert eng.train_errors(i) == int(eng.err_acc.item())
     with pytest.raises(RuntimeError):
         eng._await_loss(eng.opt_step + 1, timeout=0.2)      # a step that never ran
     # rewinding the step counter (checkpoint restore) must not match losses mailed before the rewind
@@ -142,6 +151,97 @@ def test_loss_mailbox_matches_device_accumulator():
     eng.set_state(params, slots, 3)
     tr.global_step = 3
     for i in range(4, 8):
+        l2 = l2_now()
         mailed = tr.step()
         torch.cuda.synchronize()
-        assert eng.opt_step == i and mailed == float(eng.loss_acc.item())
+        assert eng.opt_step == i and mailed == pytest.approx(float(eng.loss_acc.item()) + 5e-4 * l2, rel=2e-6)
+
+
+def test_fused_step_loss_equals_unfused_loss(monkeypatch):
+    """Same API, one meaning: the loss of the fused graph step (mailed by K1) is the loss compute_grads returns for
+    the same batch and weights, CE + 5e-4 * L2 as in the reference (mpipy.py:55-58)."""
+    monkeypatch.setenv("MTB_OVERLAP_N1", "1")        # bucketed K1 on a lone GPU too (default there: one launch)
+    dev = torch.device("cuda", 0)
+    sh = _shards(256)
+    x = torch.from_numpy(sh.train_x[:64])
+    y = torch.from_numpy(sh.train_y[:64].astype(np.int32))
+    for overlap in (True, False):
+        tr = Trainer(_cfg(batch=64, overlap=overlap), device=dev)
+        eager = tr.engine.compute_grads(x, y, 0)            # leaves the weights untouched
+        fused = tr.step(x, y)
+        assert fused == pytest.approx(eager, rel=1e-5), (overlap, fused, eager)
+        assert fused > 1.0                                   # the L2 term alone is ~3 for this model
+        tr.close()
+
+
+def test_bucketed_overlap_equals_single_launch(monkeypatch):
+    """The hidden fc bucket + closing bucket update exactly what the single whole-buffer launch updates."""
+    monkeypatch.setenv("MTB_OVERLAP_N1", "1")
+    dev = torch.device("cuda", 0)
+    sh = _shards(512)
+    out = {}
+    for overlap in (True, False):
+        tr = Trainer(_cfg(batch=64, lr=0.02, overlap=overlap, optimizer="adam", lr_decay=1.0), device=dev)
+        tr.load_data(sh)
+        losses = [tr.step() for _ in range(5)]
+        out[overlap] = (tr.engine.flat_params.clone(), [s.clone() for s in tr.engine.slots], losses)
+        assert tr.engine.launches_per_step == (13 if overlap else 12)
+        tr.close()
+    # the only difference between the two is the order in which fp32 atomics of the backward kernels land
+    a, b = out[True], out[False]
+    assert float((a[0] - b[0]).norm() / b[0].norm()) < 1e-3
+    assert np.allclose(a[2], b[2], rtol=1e-3)
+
+
+def test_bf16_gradient_wire_format_single_gpu():
+    """comm_dtype='bf16': the FC1 weight gradient is produced and consumed as bf16 (2 bytes per element on the
+    wire); everything downstream of the load stays fp32, so training follows the fp32-wire run closely."""
+    dev = torch.device("cuda", 0)
+    sh = _shards(512)
+    runs = {}
+    for wire in ("fp32", "bf16"):
+        tr = Trainer(_cfg(batch=64, lr=0.02, comm_dtype=wire), device=dev)
+        tr.load_data(sh)
+        runs[wire] = ([tr.step() for _ in range(10)], tr.engine.flat_params.clone())
+        tr.close()
+    assert runs["bf16"][0][-1] < runs["bf16"][0][0]
+    assert float((runs["bf16"][1] - runs["fp32"][1]).norm() / runs["fp32"][1].norm()) < 5e-3
+    with pytest.raises(ValueError):
+        Trainer(_cfg(dtype="fp32", comm_dtype="bf16"), device=dev)
+
+
+@pytest.mark.parametrize("size,B", [(256, 64), (200, 64), (130, 100)])
+def test_graph_captured_eval_matches_eager_predict(size, B):
+    """eval_in_batches over a resident split, whole loop in one CUDA graph (ragged tail included), gives the
+    probabilities the eager per-batch predict gives; the second call replays the graph."""
+    dev = torch.device("cuda", 0)
+    sh = _shards(512)
+    tr = Trainer(_cfg(batch=64, eval_batch=B), device=dev)
+    tr.load_data(sh)
+    for _ in range(3):
+        tr.step()
+    data = sh.train_x[:size]
+    got = tr.eval_in_batches(data)
+    assert got.shape == (size, 10) and np.allclose(got.sum(1), 1.0, atol=1e-4)
+    ref = np.concatenate([tr.engine.predict(torch.from_numpy(data[i:i + 1].repeat(B, 0))).cpu().numpy()[:1]
+                          for i in range(0, size, 37)])
+    assert np.allclose(got[::37], ref, atol=1e-5)
+    tr.step()                                                # weights move: the replay must see the new ones
+    again = tr.eval_in_batches(data)
+    assert len(tr.engine._eval_cache) == 1 and not np.array_equal(again, got)
+    ref2 = tr.engine.predict(torch.from_numpy(data[:B])).cpu().numpy()
+    assert np.allclose(again[:B], ref2, atol=1e-5)
+    tr.close()
+
+
+def test_timed_step_reports_phases(monkeypatch):
+    monkeypatch.setenv("MTB_OVERLAP_N1", "1")
+    tr = Trainer(_cfg(batch=64), device=torch.device("cuda", 0))
+    tr.load_data(_shards(256))
+    tr.step()
+    ph = tr.engine.timed_step()
+    assert tr.engine.opt_step == 2 and int(tr.engine.dev_step.item()) == 2
+    for k in ("fwd", "bwd_fc", "bwd_conv", "k1_hidden", "k1_tail", "step"):
+        assert ph[k] > 0.0, (k, ph)
+    assert ph["step"] >= ph["fwd"] + ph["bwd_fc"] + ph["bwd_conv"]
+    tr.close()
