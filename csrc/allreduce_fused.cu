@@ -19,10 +19,11 @@
 //   nvls      as two-shot, but multimem.ld_reduce pulls the switch-reduced slice in one load
 //             and multimem.st broadcasts the result (needs a multicast mapping).
 //   push      one-shot for the small bucket that closes a step: every rank STORES its gradients
-//             into a receive row on each peer (double buffered by step parity), signals once,
-//             and reduces its local rows.  One flag round instead of two: the closing round is
-//             replaced by the parity (a row is rewritten two steps later, and a rank can only
-//             get there after every peer has signalled the step in between).
+//             into a receive row on each peer as flag-in-data words (value + step tag in one
+//             16-byte store) and the receiver polls the words it needs.  No flag round at all:
+//             one one-way NVLink latency.  Rows are double buffered by step parity (a row is
+//             rewritten two steps later, which a rank only reaches after every peer has met it
+//             in the hidden bucket's barrier of the step in between).
 // Every rank sums in the same order, so replicas stay bit-identical.
 //
 // The same kernel averages PARAMETERS in place (the reference's own strategy, mpipy.py:95-153):
@@ -90,7 +91,7 @@ struct FusedParams {
   unsigned long long* loss_mail;                    // pinned host ring of {f32 loss, u32 step} words
   int loss_ring;
   int chan_base;                                    // first flag / sequence block of this launch's channel
-  float* push_recv[kMaxRanks];                      // push: every rank's receive area [2 parity][world][push_stride]
+  float* push_recv[kMaxRanks];                      // push: every rank's receive area [2 parity][world][2 * push_stride]
   long long push_stride;
   const __nv_bfloat16* grads_lp[kMaxRanks];         // bf16 wire format: gradients of [lp_begin, lp_end) live here
   const __nv_bfloat16* mc_grads_lp;
@@ -101,6 +102,7 @@ struct FusedParams {
   int l2_row;
   int l2_rows_n[kL2Rows];                           // mailing launch: entries to add per row (0 unused, 1 local, world sliced)
   int no_flags;                                     // the caller brackets this launch with barrier launches instead
+  unsigned long long* trace;                        // optional: globaltimer at the first block's start [0] and at the close [1]
   const int* err_src;                               // batch error count, mailed next to the loss
   unsigned long long* aux_mail;                     // pinned host ring of {u32 errors, u32 step} words
 };
@@ -229,11 +231,17 @@ __device__ __forceinline__ bool low_precision(const FusedParams& p, long long i)
   return i >= p.lp_begin && i < p.lp_end;
 }
 
-// One float4 of the optimizer.  g is the already averaged gradient.  l2 collects 0.5*w^2 of the
-// weights BEFORE the update over the weight-decay ranges (the L2 term of the loss, mpipy.py:57-58).
-__device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g, float& l2) {
+// One float4 of the optimizer.  g is the already averaged gradient.  l2 collects 0.5*w^2 of the weights BEFORE the
+// update over the weight-decay ranges (the L2 term of the loss, mpipy.py:57-58).
+// (Loading w / m / v for all vectors of a pass up front, next to the gradients, was measured: 128 registers, half
+// the resident threads, the 13 MB bucket 41 -> 105 us.  The loads stay here.)
+// PRE (the small, latency-bound buckets: one pass per thread, register budget irrelevant): w / m / v were loaded by the
+// caller together with the gradient, so the pass costs one memory round trip instead of two.
+template <bool PRE>
+__device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper& h, long long i, float4 g, float& l2,
+                                               float4 w, float4 m, float4 v) {
   if (p.optimizer < 0) return g;
-  float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
+  if (!PRE) w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
   if (p.n_ranges > 0 && decays(p, i)) {         // L2 term: grad += wd * w (mpipy.py:57-58)
     l2 += 0.5f * (w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w);
     g.x = fmaf(p.wd, w.x, g.x); g.y = fmaf(p.wd, w.y, g.y); g.z = fmaf(p.wd, w.z, g.z); g.w = fmaf(p.wd, w.w, g.w);
@@ -241,14 +249,16 @@ __device__ __forceinline__ float4 apply_update(const FusedParams& p, const Hyper
   if (p.optimizer == 0) {
     w.x -= h.lr * g.x; w.y -= h.lr * g.y; w.z -= h.lr * g.z; w.w -= h.lr * g.w;
   } else if (p.optimizer == 1) {                // accum = m*accum + g; w -= lr*accum (mpipy.py:65)
-    float4 m = *reinterpret_cast<float4*>(p.slot_m + i);
+    if (!PRE) m = *reinterpret_cast<float4*>(p.slot_m + i);
     m.x = fmaf(p.momentum, m.x, g.x); m.y = fmaf(p.momentum, m.y, g.y);
     m.z = fmaf(p.momentum, m.z, g.z); m.w = fmaf(p.momentum, m.w, g.w);
     *reinterpret_cast<float4*>(p.slot_m + i) = m;
     w.x -= h.lr * m.x; w.y -= h.lr * m.y; w.z -= h.lr * m.z; w.w -= h.lr * m.w;
   } else {
-    float4 m = *reinterpret_cast<float4*>(p.slot_m + i);
-    float4 v = *reinterpret_cast<float4*>(p.slot_v + i);
+    if (!PRE) {
+      m = *reinterpret_cast<float4*>(p.slot_m + i);
+      v = *reinterpret_cast<float4*>(p.slot_v + i);
+    }
     const float b1 = p.beta1, b2 = p.beta2, c1 = 1.f - b1, c2 = 1.f - b2;
     m.x = b1 * m.x + c1 * g.x; m.y = b1 * m.y + c1 * g.y; m.z = b1 * m.z + c1 * g.z; m.w = b1 * m.w + c1 * g.w;
     v.x = b2 * v.x + c2 * g.x * g.x; v.y = b2 * v.y + c2 * g.y * g.y;
@@ -267,33 +277,50 @@ __device__ __forceinline__ uint2 to_bf16x4(float4 w) {
 
 enum Kind { kLocal = 0, kOneShot = 1, kTwoShot = 2, kNvls = 3, kPush = 4 };
 
-// Vectors [lo, hi) of the bucket, kUnroll per thread per pass: all reductions (peer loads or
-// switch-reduced multimem loads) of a pass are issued before any of them is used, which is what
-// keeps enough bytes in flight to cover NVLink latency.  `recv` (push only): this rank's receive
-// rows of the current parity, [world][push_stride].
-template <int KIND>
+// Flag-in-data words of the push bucket (the "LL" idea): a 16-byte store carries two floats and the step tag twice,
+// {d0, tag, d1, tag}; the receiver polls the data itself until both tags match, so there is no fence, no separate
+// flag and no second trip: one one-way NVLink latency from the sender's store to the receiver's use.
+__device__ __forceinline__ void st_ll(uint4* dst, float a, float b, uint32_t tag) {
+  asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(__float_as_uint(a)), "r"(tag),
+               "r"(__float_as_uint(b)), "r"(tag) : "memory");
+}
+__device__ __forceinline__ uint4 ld_ll(const uint4* src) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(src) : "memory");
+  return v;
+}
+
+// Vectors [lo, hi) of the bucket, kUnroll per thread per pass: all reductions (peer loads or switch-reduced multimem
+// loads) of a pass are issued before any of them is used, which is what keeps enough bytes in flight to cover NVLink
+// latency.  `recv` (push only): this rank's receive rows of the current parity, [world][2 * push_stride] floats of LL
+// words.
+template <int KIND, bool PRE>
 __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, long long lo, long long hi, float& l2,
-                                          const float* recv = nullptr) {
+                                          const uint4* recv = nullptr, uint32_t tag = 0) {
   constexpr int kUnroll = 4;
+  constexpr int kPre = PRE ? kUnroll : 1;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const bool has_lp = p.lp_end > p.lp_begin;
   for (long long v0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; v0 < hi; v0 += stride * kUnroll) {
-    float4 g[kUnroll];
+    float4 g[kUnroll], pw[kPre], pm[kPre], pv[kPre];
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       const long long v = v0 + u * stride;
       g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (PRE) pw[u % kPre] = pm[u % kPre] = pv[u % kPre] = g[u];
       if (v < hi) {
         const long long i = p.offset + (v << 2);
+        if (PRE && p.optimizer >= 0) {
+          pw[u % kPre] = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
+          if (p.optimizer >= 1) pm[u % kPre] = *reinterpret_cast<const float4*>(p.slot_m + i);
+          if (p.optimizer == 2) pv[u % kPre] = *reinterpret_cast<const float4*>(p.slot_v + i);
+        }
         if (KIND == kLocal) {
           g[u] = (has_lp && low_precision(p, i)) ? ld_peer_bf16x4(p.grads_lp[0] + i)
                                                  : *reinterpret_cast<const float4*>(p.grads[0] + i);
         } else if (KIND == kPush) {
-          for (int r = 0; r < p.world; ++r) {       // rank order; my own row is the gradient buffer itself
-            const float4 t = r == p.rank ? *reinterpret_cast<const float4*>(p.grads[r] + i)
-                                         : ld_peer_f4(recv + r * p.push_stride + (v << 2));
-            g[u].x += t.x; g[u].y += t.y; g[u].z += t.z; g[u].w += t.w;
-          }
+          g[u] = *reinterpret_cast<const float4*>(p.grads[p.rank] + i);        // peers' rows are polled below
         } else if ((KIND == kNvls || KIND == kTwoShot) && p.n_prered > 0 && prereduced(p, i)) {
           g[u] = ld_peer_f4(p.grads[p.rank] + i);            // summed in place by the producers' epilogues
           *reinterpret_cast<float4*>(const_cast<float*>(p.grads[p.rank]) + i) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -316,6 +343,33 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
         }
       }
     }
+    if (KIND == kPush) {
+      // sum in rank order (my own gradient takes its place in the sequence), polling each peer's LL words
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long v = v0 + u * stride;
+        if (v >= hi) continue;
+        const float4 mine = g[u];
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        const long long t0 = clock64();
+        for (int r = 0; r < p.world; ++r) {
+          float4 t = mine;
+          if (r != p.rank) {
+            const uint4* src = recv + (long long)r * (p.push_stride >> 1) + (v << 1);
+            uint4 a, b;
+            while (true) {
+              a = ld_ll(src);
+              b = ld_ll(src + 1);
+              if (a.y == tag && a.w == tag && b.y == tag && b.w == tag) break;
+              if (clock64() - t0 > kSpinLimit) { atomicExch(p.status, MTB_E_TIMEOUT); break; }
+            }
+            t = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+          }
+          acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
+        g[u] = acc;
+      }
+    }
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       const long long v = v0 + u * stride;
@@ -323,21 +377,21 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
       const long long i = p.offset + (v << 2);
       float4 gs = g[u];
       gs.x *= p.scale; gs.y *= p.scale; gs.z *= p.scale; gs.w *= p.scale;
-      const float4 w = apply_update(p, h, i, gs, l2);
-      const uint2 wb = to_bf16x4(w);
+      const float4 wn = apply_update<PRE>(p, h, i, gs, l2, pw[u % kPre], pm[u % kPre], pv[u % kPre]);
+      const uint2 wb = to_bf16x4(wn);
       if (KIND == kLocal || KIND == kOneShot || KIND == kPush) {
-        *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
+        *reinterpret_cast<float4*>(p.params[p.rank] + i) = wn;
         if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = wb;
       } else if (KIND == kNvls) {
         // sharded master: my fp32 copy is the only current one, peers get the bf16 shadow
-        if (master_sharded(p, i)) *reinterpret_cast<float4*>(p.params[p.rank] + i) = w;
-        else multimem_st_f4(p.mc_params + i, w);
+        if (master_sharded(p, i)) *reinterpret_cast<float4*>(p.params[p.rank] + i) = wn;
+        else multimem_st_f4(p.mc_params + i, wn);
         if (p.mc_shadow) multimem_st_bf16x4(p.mc_shadow + i, wb);
       } else {
         const bool sharded = master_sharded(p, i);
         for (int r = 0; r < p.world; ++r) {
           if (p.dst_mask != 0u && !((p.dst_mask >> r) & 1u)) continue;
-          if (!sharded || r == p.rank) *reinterpret_cast<float4*>(p.params[r] + i) = w;
+          if (!sharded || r == p.rank) *reinterpret_cast<float4*>(p.params[r] + i) = wn;
           if (p.shadow[r]) *reinterpret_cast<uint2*>(p.shadow[r] + i) = wb;
         }
       }
@@ -345,14 +399,18 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
   }
 }
 
-// push, phase 1: my gradients of this block's vectors into my row on every peer
-__device__ __forceinline__ void push_range(const FusedParams& p, long long vec_total, int parity) {
+// push, phase 1: my gradients of this block's vectors, as LL words, into my row on every peer
+__device__ __forceinline__ void push_range(const FusedParams& p, long long vec_total, int parity, uint32_t tag) {
   const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long row = ((long long)parity * p.world + p.rank) * p.push_stride;
+  const long long row = ((long long)parity * p.world + p.rank) * (p.push_stride >> 1);     // in uint4 units
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < vec_total; v += stride) {
     const float4 g = *reinterpret_cast<const float4*>(p.grads[p.rank] + p.offset + (v << 2));
     for (int r = 0; r < p.world; ++r)
-      if (r != p.rank) st_peer_f4(p.push_recv[r] + row + (v << 2), g);
+      if (r != p.rank) {
+        uint4* dst = reinterpret_cast<uint4*>(p.push_recv[r]) + row + (v << 1);
+        st_ll(dst, g.x, g.y, tag);
+        st_ll(dst + 1, g.z, g.w, tag);
+      }
   }
 }
 
@@ -360,8 +418,8 @@ __device__ __forceinline__ unsigned long long tagged(uint32_t tag, float v) {
   return (static_cast<unsigned long long>(tag) << 32) | __float_as_uint(v);
 }
 
-__global__ void __launch_bounds__(256, 4)
-fused_allreduce_update_kernel(const FusedParams p) {
+template <bool PRE>
+__device__ __forceinline__ void fused_body(const FusedParams& p) {
   const int b = blockIdx.x;
   const int fb = p.chan_base + b;                    // this block's flag / sequence slot
   __shared__ uint32_t s_seq;
@@ -371,6 +429,11 @@ fused_allreduce_update_kernel(const FusedParams p) {
   if (threadIdx.x == 0) s_seq = (p.world > 1 && !p.no_flags) ? p.seq[fb] : 0u;
   __syncthreads();
   const uint32_t seq = s_seq;
+  if (p.trace != nullptr && b == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[0] = t;
+  }
   const long long step = p.step_ptr ? *p.step_ptr : 0;
   // what the closing warp mails was final before this launch began: fetch it now, off the closing chain's critical path
   float loss_in = 0.f;
@@ -387,27 +450,28 @@ fused_allreduce_update_kernel(const FusedParams p) {
   uint32_t rounds = 0;
 
   if (!multi) {
-    run_range<kLocal>(p, h, 0, vec_total, l2);
+    run_range<kLocal, PRE>(p, h, 0, vec_total, l2);
   } else if (p.algo == 3) {
-    // one flag round: data first, then the flag (release after a system fence), then the local reduction
+    // no flag round at all: the pushed words carry the step's tag and the receiver polls them
     const int parity = (int)(step & 1);
-    push_range(p, vec_total, parity);
-    cross_gpu_barrier(p, fb, seq + 1, true);
-    rounds = 1;
-    run_range<kPush>(p, h, 0, vec_total, l2, p.push_recv[p.rank] + (long long)parity * p.world * p.push_stride);
+    const uint32_t tag = static_cast<uint32_t>(step + 1);
+    push_range(p, vec_total, parity, tag);
+    run_range<kPush, PRE>(p, h, 0, vec_total, l2,
+                     reinterpret_cast<const uint4*>(p.push_recv[p.rank]) + (long long)parity * p.world * (p.push_stride >> 1),
+                     tag);
   } else {
     // every peer's gradients are complete (with pre-reduced ranges some of them were written into MY memory by
     // peers' kernels: the fence makes this rank's own remote additions globally visible before it signals)
     if (!p.no_flags) cross_gpu_barrier(p, fb, seq + 1, p.n_prered > 0);
     if (p.algo == 0) {
-      run_range<kOneShot>(p, h, 0, vec_total, l2);
+      run_range<kOneShot, PRE>(p, h, 0, vec_total, l2);
     } else {
       // two-shot / nvls: this rank owns one contiguous slice
       const long long per = (vec_total + p.world - 1) / p.world;
       const long long lo = per * p.rank < vec_total ? per * p.rank : vec_total;
       const long long hi = lo + per < vec_total ? lo + per : vec_total;
-      if (p.algo == 2) run_range<kNvls>(p, h, lo, hi, l2);
-      else run_range<kTwoShot>(p, h, lo, hi, l2);
+      if (p.algo == 2) run_range<kNvls, PRE>(p, h, lo, hi, l2);
+      else run_range<kTwoShot, PRE>(p, h, lo, hi, l2);
     }
     // peers are done reading my grads (loads have retired: their values were consumed) and, in the
     // two-shot / nvls forms, done writing my params (needs the fence)
@@ -433,10 +497,14 @@ fused_allreduce_update_kernel(const FusedParams p) {
     s_last = 0;
     if (p.done_counter != nullptr) {
       // every block read the step counter at its start; the last one to finish closes the launch
-      __threadfence();
-      if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
-        *p.done_counter = 0u;
+      if (gridDim.x == 1) {
         s_last = 1;
+      } else {
+        __threadfence();
+        if (atomicAdd(p.done_counter, 1u) == gridDim.x - 1) {
+          *p.done_counter = 0u;
+          s_last = 1;
+        }
       }
     }
   }
@@ -446,6 +514,11 @@ fused_allreduce_update_kernel(const FusedParams p) {
   // walking hundreds of block partials (or 24 peer slots) pays one L2 round trip per element, tens of microseconds.
   const int lane = threadIdx.x;
   __threadfence();
+  if (p.trace != nullptr && lane == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[1] = t;
+  }
   const uint32_t tag = static_cast<uint32_t>(step + 1);
   float total = 0.f;
   if (want_l2) {
@@ -498,6 +571,12 @@ fused_allreduce_update_kernel(const FusedParams p) {
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.loss_mail + slot), "l"(tagged(tag, loss)) : "memory");
   }
 }
+
+// Two builds of the same body.  The bulk kernel is capped at 64 registers so that four 256-thread blocks (or many
+// narrow ones next to a convolution CTA) share an SM: a 13 MB bucket is bandwidth-delay bound and wants threads.  The
+// small-bucket kernel runs one pass per thread and is pure latency: it loads the parameter state with the gradients.
+__global__ void __launch_bounds__(256, 4) fused_allreduce_update_kernel(const FusedParams p) { fused_body<false>(p); }
+__global__ void __launch_bounds__(256, 2) fused_small_bucket_kernel(const FusedParams p) { fused_body<true>(p); }
 
 // The stand-alone barrier has a flag block of its own (the last one), so it never shares a sequence number with a
 // fused launch that may be in flight on another stream.
@@ -563,6 +642,7 @@ static int fill(const mtb_fused_args* a, FusedParams* p) {
   p->loss_ring = a->loss_ring;
   p->chan_base = a->chan ? kChan1Base : 0;
   p->no_flags = a->no_flags;
+  p->trace = reinterpret_cast<unsigned long long*>(a->trace);
   MTB_REQUIRE(!a->no_flags || a->algo != 3, "fused: push carries its own flag round");
   p->push_stride = a->push_stride;
   for (int r = 0; r < kMaxRanks; ++r) {
@@ -627,7 +707,9 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   const bool flags = p.world > 1 && !p.no_flags;
   if (flags && grid > (a->chan ? kChan1Blocks : kChan1Base)) grid = a->chan ? kChan1Blocks : kChan1Base;
   if (grid > kMaxL2Blocks) grid = kMaxL2Blocks;
-  MTB_CUDA_CHECK(mtb::launch(fused_allreduce_update_kernel, dim3(grid), dim3(block), 0, stream, p));
+  const bool small = p.count * 4 <= (1ll << 20) && grid * block * 4ll >= vecs;       // at most one pass per thread
+  MTB_CUDA_CHECK(mtb::launch(small ? fused_small_bucket_kernel : fused_allreduce_update_kernel, dim3(grid), dim3(block), 0,
+                             stream, p));
   return 0;
 }
 
@@ -648,6 +730,7 @@ int mtb_advance_step(long long* step_ptr, cudaStream_t stream) {
 }
 
 int mtb_fused_max_blocks(void) { return kMaxBlocks; }
+int mtb_fused_args_size(void) { return (int)sizeof(mtb_fused_args); }
 int mtb_fused_max_l2_blocks(void) { return kMaxL2Blocks; }
 int mtb_fused_flag_bytes(void) { return kMaxBlocks * kMaxRanks * (int)sizeof(uint32_t); }
 

@@ -237,10 +237,12 @@ typedef struct mtb_fused_args {
   int no_flags;         /* 1: no flag rounds inside this launch; the caller runs mtb_p2p_barrier before it (peers' gradients
                          * complete) and after it (peer loads and stores done) on the same stream.  Lets the launch use any
                          * number of short-lived blocks (grid < 0: one pass per block). */
-  /* algo 3, "push": one-shot for a small bucket with ONE flag round.  Every rank stores its gradients into its row of
-   * each peer's receive area (rows double buffered by the parity of *step_ptr), signals, and reduces its local rows. */
-  void* push_recv[16];  /* every rank's receive area, peer-mapped: [2][world][push_stride] floats */
-  long long push_stride;/* floats per row, >= count, multiple of 4 */
+  /* algo 3, "push": one-shot for a small bucket with NO flag round.  Every rank stores its gradients into its row of
+   * each peer's receive area as flag-in-data words {f32, tag, f32, tag} (tag = *step_ptr + 1; rows double buffered by the
+   * step's parity); the receiver polls the words it needs until their tags match and reduces in rank order.  The area
+   * must be cleared (by its owner, between barriers) whenever *step_ptr is moved backwards. */
+  void* push_recv[16];  /* every rank's receive area, peer-mapped: [2][world][2 * push_stride] floats, zeroed */
+  long long push_stride;/* payload floats per row, >= count, multiple of 4 */
   /* bf16 gradient wire format: inside [lp_begin, lp_end) gradients are read as bf16 from grads_lp (peer loads, or
    * multimem.ld_reduce with fp32 accumulation in the switch) and everything after the load stays fp32. */
   const void* grads_lp[16];
@@ -256,6 +258,7 @@ typedef struct mtb_fused_args {
   void* l2_slots[16];   /* every rank's uint64[4][16], peer-mapped */
   int l2_row;
   int l2_rows_n[4];     /* entries to add per row: 0 unused, 1 local, world = one per slice owner */
+  void* trace;          /* optional uint64[2]: %globaltimer (ns) when the launch's first block starts and when it closes */
   const void* err_src;  /* int32 error count of the batch, mailed as {step : errors} into aux_mail (same ring size) */
   void* aux_mail;
 } mtb_fused_args;
@@ -263,6 +266,7 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream);
 int mtb_p2p_barrier(const mtb_fused_args* a, cudaStream_t stream);          /* comm.Barrier(), mpipy.py:93 */
 int mtb_advance_step(long long* step_ptr, cudaStream_t stream);             /* global_step=iter_, mpipy.py:66 */
 int mtb_fused_max_blocks(void);
+int mtb_fused_args_size(void);          /* sizeof(mtb_fused_args), for bindings to check their layout against */
 int mtb_fused_max_l2_blocks(void);      /* capacity needed for l2_blocks, in floats */
 int mtb_fused_flag_bytes(void);
 

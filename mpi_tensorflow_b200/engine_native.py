@@ -69,9 +69,10 @@ class NativeEngine:
                          and cfg.comm_algo not in ("oneshot", "push") and not self._lp)
         # bucketed overlap (default): the fc bucket's fused allreduce+update runs on the comm stream under the
         # convolution backward; the reduce-scatter GEMM needs the single whole-buffer launch instead
-        # (on a lone GPU there is no flag round or NVLink latency to hide: one launch there unless MTB_OVERLAP_N1=1)
+        # (a lone GPU has no flag round or NVLink latency to hide, but the 72 MB of the update itself still hide
+        # under the convolutions: 213.6 vs 219.3 us per step; MTB_OVERLAP_N1=0 gives the single launch back)
         self._overlap = (bool(cfg.overlap) and not self._rs_mode
-                         and (self.world > 1 or os.environ.get("MTB_OVERLAP_N1") == "1"))
+                         and (self.world > 1 or os.environ.get("MTB_OVERLAP_N1", "1") != "0"))
         self._rs_active = False                  # True only inside the fused step body
         self._rs_dirty = True                    # owners' fc1 slices must be zero when a fused step starts
         if self._rs_mode:
@@ -144,12 +145,13 @@ class NativeEngine:
                 self._slot_mc.append(mc)
             else:
                 self.slots.append(torch.zeros(n, device=dev))
-        # receive rows of the "push" tail bucket: [2 parity][world][stride] floats on every rank
+        # receive rows of the "push" tail bucket: [2 parity][world][stride] (value, tag) pairs on every rank
         self._tail_hi = self.spec.param("fc1_weight").offset
         self._push_stride = (self._tail_hi + 3) // 4 * 4
-        self._push = self.p2p.alloc_symmetric(2 * self.world * self._push_stride * 4) if multi else None
+        self._push = self.p2p.alloc_symmetric(2 * self.world * self._push_stride * 8) if multi else None
         self._sliced: Dict = {}                  # (lo, hi) of every owner-sliced peer launch -> algo
         self._l2_blocks = torch.zeros(2, N.lib().mtb_fused_max_l2_blocks(), device=dev)
+        self._trace = torch.zeros(3, 2, dtype=torch.int64, device=dev) if os.environ.get("MTB_K1_TRACE") == "1" else None
         self._l2_slots = torch.zeros(4 * 16, dtype=torch.int64, device=dev)          # world-1 stand-in for the p2p slots
         self.dev_step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.loss_acc = torch.zeros(1, device=dev)
@@ -244,6 +246,14 @@ class NativeEngine:
     def synchronize(self):
         torch.cuda.current_stream().synchronize()
 
+    def _reset_push(self):
+        """Clear the push bucket's receive rows: their words are tagged with the step number, so whenever the step
+        counter moves backwards (checkpoint restore, the rolled-back warm-up step before a graph capture) a stale
+        row could pass for the new step's.  Callers put a barrier between this and the next step."""
+        if self._push is not None:
+            self._push.local.zero_()
+            torch.cuda.synchronize()
+
     # -- state that the two-shot / nvls update keeps only with the owner of each slice ------------
     def _owned_ranges(self):
         """Element ranges of the flat buffers whose optimizer state (and sharded fp32 master) only THIS rank
@@ -322,6 +332,7 @@ class NativeEngine:
         self.synchronize()
         self._mail.zero_()                        # a rewound counter must not match losses mailed before
         self._aux.zero_()
+        self._reset_push()
 
     # ------------------------------------------------------------------ data
     def attach_dataset(self, shards):
@@ -631,6 +642,8 @@ class NativeEngine:
             self._slots_dirty = True                                   # slots of non-owned slices are not maintained
         a.grid, a.block, a.chan = grid, block, chan
         a.no_flags = int(no_flags and peers and a.algo != 3)
+        if self._trace is not None:
+            a.trace = self._trace[l2_row if (advance or chan == 0) else 2].data_ptr()
         if self._rs_active and sliced:
             fc1w = self.spec.param("fc1_weight")
             a.n_prered = 1
@@ -763,13 +776,13 @@ class NativeEngine:
 
     def _hidden_launch(self, peers: bool, lo: int, hi: int, row: int) -> bool:
         """One bucket's fused allreduce+update on the comm stream, shaped to run UNDER the persistent convolution
-        kernels: many short-lived narrow blocks (64 threads, one 4-vector pass each) that fit into whatever registers
+        kernels: many short-lived narrow blocks (one warp, one 4-vector pass each) that fit into whatever registers
         the resident convolution CTA leaves free and give them back every few microseconds, instead of blocks parked on
         the SMs for the whole transfer.  That needs more blocks than there are flag slots, so the two flag rounds
         are their own one-warp launches before and after the data launch."""
         multi = peers and self.p2p is not None and self.world > 1
         grid = int(os.environ.get("MTB_K1_GRID_A", "-1"))
-        block = int(os.environ.get("MTB_K1_BLOCK_A", "64"))
+        block = int(os.environ.get("MTB_K1_BLOCK_A", "32"))
         probe = os.environ.get("MTB_K1_PROBE")              # "fat:60" / "lean:60": occupancy probe instead of K1 (scripts)
         with torch.cuda.stream(self._comm_stream):
             if probe:
@@ -969,6 +982,7 @@ class NativeEngine:
         torch.cuda.synchronize()
         self._mail[self.opt_step % self._MAIL_RING] = 0        # the rolled-back warm-up step mailed a loss too
         self._aux[self.opt_step % self._MAIL_RING] = 0
+        self._reset_push()
         if self.p2p is not None:
             self.p2p.barrier()
         g = torch.cuda.CUDAGraph()

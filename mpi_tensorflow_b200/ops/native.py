@@ -40,7 +40,7 @@ class FusedArgs(C.Structure):
         ("grads_lp", vp * 16), ("mc_grads_lp", vp), ("lp_begin", i64), ("lp_end", i64),
         ("dst_mask", C.c_uint),
         ("l2_blocks", vp), ("l2_slots", vp * 16), ("l2_row", i32), ("l2_rows_n", i32 * 4),
-        ("err_src", vp), ("aux_mail", vp),
+        ("trace", vp), ("err_src", vp), ("aux_mail", vp),
     ]
 
 
@@ -141,6 +141,9 @@ def lib() -> C.CDLL:
     L.mtb_conv2_wgrad_workspace_bytes.argtypes = [i32]
     L.mtb_conv2_wgrad_workspace_bytes.restype = C.c_size_t
     L.mtb_fused_max_blocks.restype = i32
+    L.mtb_fused_args_size.restype = i32
+    if L.mtb_fused_args_size() != C.sizeof(FusedArgs):
+        raise ImportError(f"FusedArgs layout drifted from include/mtb200.h: {C.sizeof(FusedArgs)} vs {L.mtb_fused_args_size()} bytes")
     L.mtb_fused_max_l2_blocks.restype = i32
     L.mtb_fused_flag_bytes.restype = i32
     _LIB = L
