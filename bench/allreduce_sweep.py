@@ -106,12 +106,20 @@ def main():
             ms = timed(fn2, comm, iters)
             rec["nccl_us"] = ms * 1e3
             rec["nccl_busbw_gbs"] = 2 * (n - 1) / n * size / (ms * 1e-3) / 1e9
-        best = min(v for k, v in rec.items() if k.startswith("p2p") and k.endswith("_us"))
-        rec["p2p_best_us"] = best
+        times = {k[:-3]: v for k, v in rec.items() if k.startswith("p2p") and k.endswith("_us")}
+        best_name = min(times, key=times.get)
+        rec["p2p_best"], rec["p2p_best_us"] = best_name, times[best_name]
         if n > 1:
-            floor_us = max(2 * (n - 1) / n * size / (LINK_GBS * 1e9) * 1e6, 0.0)
-            rec["link_floor_us"] = floor_us
-            rec["p2p_frac_of_link_roofline"] = floor_us / best
+            # Link-time floor of EACH algorithm for its own traffic (bytes over one direction of NVLink at the measured
+            # 770 GB/s): one-shot pulls the whole message from N-1 peers; two-shot moves (N-1)/N of it in and as much
+            # out again, back to back; with the in-switch reduction a GPU sends its (N-1)/N share of the reads up while
+            # the reduced slice comes down, then broadcasts its slice: S/N * (N-1) up twice over ~ S each way.
+            floors = {"p2p_oneshot": (n - 1) * size, "p2p_twoshot": 2 * (n - 1) / n * size, "p2p_nvls": size}
+            for name, t in times.items():
+                fl = floors[name] / (LINK_GBS * 1e9) * 1e6
+                rec[name + "_floor_us"] = fl
+                rec[name + "_frac_of_floor"] = fl / t
+            rec["p2p_best_frac_of_its_floor"] = rec[best_name + "_frac_of_floor"]
         rows.append(rec)
         if r == 0:
             print(json.dumps(rec), flush=True)

@@ -275,7 +275,7 @@ __device__ __forceinline__ uint2 to_bf16x4(float4 w) {
   return make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
 }
 
-enum Kind { kLocal = 0, kOneShot = 1, kTwoShot = 2, kNvls = 3, kPush = 4 };
+enum Kind { kLocal = 0, kOneShot = 1, kTwoShot = 2, kNvls = 3 };
 
 // Flag-in-data words of the push bucket (the "LL" idea): a 16-byte store carries two floats and the step tag twice,
 // {d0, tag, d1, tag}; the receiver polls the data itself until both tags match, so there is no fence, no separate
@@ -293,11 +293,9 @@ __device__ __forceinline__ uint4 ld_ll(const uint4* src) {
 
 // Vectors [lo, hi) of the bucket, kUnroll per thread per pass: all reductions (peer loads or switch-reduced multimem
 // loads) of a pass are issued before any of them is used, which is what keeps enough bytes in flight to cover NVLink
-// latency.  `recv` (push only): this rank's receive rows of the current parity, [world][2 * push_stride] floats of LL
-// words.
+// latency.
 template <int KIND, bool PRE>
-__device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, long long lo, long long hi, float& l2,
-                                          const uint4* recv = nullptr, uint32_t tag = 0) {
+__device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, long long lo, long long hi, float& l2) {
   constexpr int kUnroll = 4;
   constexpr int kPre = PRE ? kUnroll : 1;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -319,8 +317,6 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
         if (KIND == kLocal) {
           g[u] = (has_lp && low_precision(p, i)) ? ld_peer_bf16x4(p.grads_lp[0] + i)
                                                  : *reinterpret_cast<const float4*>(p.grads[0] + i);
-        } else if (KIND == kPush) {
-          g[u] = *reinterpret_cast<const float4*>(p.grads[p.rank] + i);        // peers' rows are polled below
         } else if ((KIND == kNvls || KIND == kTwoShot) && p.n_prered > 0 && prereduced(p, i)) {
           g[u] = ld_peer_f4(p.grads[p.rank] + i);            // summed in place by the producers' epilogues
           *reinterpret_cast<float4*>(const_cast<float*>(p.grads[p.rank]) + i) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -343,33 +339,6 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
         }
       }
     }
-    if (KIND == kPush) {
-      // sum in rank order (my own gradient takes its place in the sequence), polling each peer's LL words
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const long long v = v0 + u * stride;
-        if (v >= hi) continue;
-        const float4 mine = g[u];
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        const long long t0 = clock64();
-        for (int r = 0; r < p.world; ++r) {
-          float4 t = mine;
-          if (r != p.rank) {
-            const uint4* src = recv + (long long)r * (p.push_stride >> 1) + (v << 1);
-            uint4 a, b;
-            while (true) {
-              a = ld_ll(src);
-              b = ld_ll(src + 1);
-              if (a.y == tag && a.w == tag && b.y == tag && b.w == tag) break;
-              if (clock64() - t0 > kSpinLimit) { atomicExch(p.status, MTB_E_TIMEOUT); break; }
-            }
-            t = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
-          }
-          acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-        }
-        g[u] = acc;
-      }
-    }
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       const long long v = v0 + u * stride;
@@ -379,7 +348,7 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
       gs.x *= p.scale; gs.y *= p.scale; gs.z *= p.scale; gs.w *= p.scale;
       const float4 wn = apply_update<PRE>(p, h, i, gs, l2, pw[u % kPre], pm[u % kPre], pv[u % kPre]);
       const uint2 wb = to_bf16x4(wn);
-      if (KIND == kLocal || KIND == kOneShot || KIND == kPush) {
+      if (KIND == kLocal || KIND == kOneShot) {
         *reinterpret_cast<float4*>(p.params[p.rank] + i) = wn;
         if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = wb;
       } else if (KIND == kNvls) {
@@ -399,18 +368,75 @@ __device__ __forceinline__ void run_range(const FusedParams& p, const Hyper& h, 
   }
 }
 
-// push, phase 1: my gradients of this block's vectors, as LL words, into my row on every peer
-__device__ __forceinline__ void push_range(const FusedParams& p, long long vec_total, int parity, uint32_t tag) {
+// The push bucket, ONE vector per thread per iteration: store my gradient (as LL words) into my row on every peer,
+// request my own parameter state, then poll the peers' words for this vector - all of them at once, eight peers per
+// round trip, not one after the other (7 peers x 4 vectors polled in sequence cost 35 us on 8 GPUs) - and sum in rank
+// order with my own gradient in its place.  Rows: [parity][source rank][push_stride / 2] uint4.
+template <bool PRE>
+__device__ __forceinline__ void push_update_range(const FusedParams& p, const Hyper& h, long long vec_total, int parity,
+                                                  uint32_t tag, float& l2) {
   const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long row = ((long long)parity * p.world + p.rank) * (p.push_stride >> 1);     // in uint4 units
+  const long long rowq = p.push_stride >> 1;
+  const uint4* recv = reinterpret_cast<const uint4*>(p.push_recv[p.rank]) + (long long)parity * p.world * rowq;
+  const long long myrow = ((long long)parity * p.world + p.rank) * rowq;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < vec_total; v += stride) {
-    const float4 g = *reinterpret_cast<const float4*>(p.grads[p.rank] + p.offset + (v << 2));
+    const long long i = p.offset + (v << 2);
+    const float4 mine = *reinterpret_cast<const float4*>(p.grads[p.rank] + i);
     for (int r = 0; r < p.world; ++r)
       if (r != p.rank) {
-        uint4* dst = reinterpret_cast<uint4*>(p.push_recv[r]) + row + (v << 1);
-        st_ll(dst, g.x, g.y, tag);
-        st_ll(dst + 1, g.z, g.w, tag);
+        uint4* dst = reinterpret_cast<uint4*>(p.push_recv[r]) + myrow + (v << 1);
+        st_ll(dst, mine.x, mine.y, tag);
+        st_ll(dst + 1, mine.z, mine.w, tag);
       }
+    float4 w = make_float4(0.f, 0.f, 0.f, 0.f), m = w, sv = w;
+    if (p.optimizer >= 0) {
+      w = *reinterpret_cast<const float4*>(p.params[p.rank] + i);
+      if (p.optimizer >= 1) m = *reinterpret_cast<const float4*>(p.slot_m + i);
+      if (p.optimizer == 2) sv = *reinterpret_cast<const float4*>(p.slot_v + i);
+    }
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long t0 = clock64();
+    for (int r0 = 0; r0 < p.world; r0 += 8) {
+      uint4 a[8], b[8];
+      bool ok;
+      do {
+        ok = true;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int r = r0 + k;
+          if (r < p.world && r != p.rank) {
+            const uint4* src = recv + (long long)r * rowq + (v << 1);
+            a[k] = ld_ll(src);
+            b[k] = ld_ll(src + 1);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int r = r0 + k;
+          if (r < p.world && r != p.rank)
+            ok = ok && a[k].y == tag && a[k].w == tag && b[k].y == tag && b[k].w == tag;
+        }
+        if (!ok && clock64() - t0 > kSpinLimit) {
+          atomicExch(p.status, MTB_E_TIMEOUT);
+          break;
+        }
+      } while (!ok);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int r = r0 + k;
+        if (r < p.world) {
+          float4 t = mine;
+          if (r != p.rank)
+            t = make_float4(__uint_as_float(a[k].x), __uint_as_float(a[k].z), __uint_as_float(b[k].x),
+                            __uint_as_float(b[k].z));
+          acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
+      }
+    }
+    acc.x *= p.scale; acc.y *= p.scale; acc.z *= p.scale; acc.w *= p.scale;
+    const float4 wn = apply_update<true>(p, h, i, acc, l2, w, m, sv);
+    *reinterpret_cast<float4*>(p.params[p.rank] + i) = wn;
+    if (p.shadow[p.rank]) *reinterpret_cast<uint2*>(p.shadow[p.rank] + i) = to_bf16x4(wn);
   }
 }
 
@@ -455,10 +481,7 @@ __device__ __forceinline__ void fused_body(const FusedParams& p) {
     // no flag round at all: the pushed words carry the step's tag and the receiver polls them
     const int parity = (int)(step & 1);
     const uint32_t tag = static_cast<uint32_t>(step + 1);
-    push_range(p, vec_total, parity, tag);
-    run_range<kPush, PRE>(p, h, 0, vec_total, l2,
-                     reinterpret_cast<const uint4*>(p.push_recv[p.rank]) + (long long)parity * p.world * (p.push_stride >> 1),
-                     tag);
+    if constexpr (PRE) push_update_range<PRE>(p, h, vec_total, parity, tag, l2);      // (only built into the small-bucket kernel)
   } else {
     // every peer's gradients are complete (with pre-reduced ranges some of them were written into MY memory by
     // peers' kernels: the fence makes this rank's own remote additions globally visible before it signals)
@@ -698,7 +721,8 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   if (block < 32) block = 32;
   block = (block + 31) / 32 * 32;
   // one pass = 4 vectors (64 bytes) per thread; another block (and its flag round) pays off after that
-  long long need = (vecs + 4 * block - 1) / (4 * block);
+  const int per_thread = (p.world > 1 && p.algo == 3) ? 1 : 4;      // push polls all peers per vector: one vector each
+  long long need = (vecs + per_thread * block - 1) / (per_thread * block);
   if (need < 1) need = 1;
   // grid < 0: one pass per block ("short-lived blocks": a launch that runs UNDER other kernels must not park blocks
   // on an SM for its whole duration; leftover register space is handed back every few microseconds)
@@ -707,7 +731,8 @@ int mtb_fused_allreduce_update(const mtb_fused_args* a, cudaStream_t stream) {
   const bool flags = p.world > 1 && !p.no_flags;
   if (flags && grid > (a->chan ? kChan1Blocks : kChan1Base)) grid = a->chan ? kChan1Blocks : kChan1Base;
   if (grid > kMaxL2Blocks) grid = kMaxL2Blocks;
-  const bool small = p.count * 4 <= (1ll << 20) && grid * block * 4ll >= vecs;       // at most one pass per thread
+  const bool small = (p.world > 1 && p.algo == 3) ||
+                     (p.count * 4 <= (1ll << 20) && grid * block * 4ll >= vecs);       // at most one pass per thread
   MTB_CUDA_CHECK(mtb::launch(small ? fused_small_bucket_kernel : fused_allreduce_update_kernel, dim3(grid), dim3(block), 0,
                              stream, p));
   return 0;
