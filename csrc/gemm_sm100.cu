@@ -50,6 +50,21 @@ struct GemmParams {
   float* rs_out[16];                   // every rank's flat gradient buffer (peer-mapped)
   int rs_staged;                       // 1: transpose each 32x32 chunk through smem so a warp adds whole 128-byte row segments
 #endif
+  // Implicit-GEMM 5x5 SAME convolution (CONV template parameter): the im2col matrix is never built; the producer
+  // addresses the NHWC activation tensor directly through a 4-D tensor map (out-of-bounds box coordinates give the zero
+  // padding).  Image rows are walked 16 columns wide (14 real + 2 zero-filled), so that a box is a rectangle of pixels.
+  //   CONV 1 (fprop / dgrad): GEMM row = output pixel.  M tile = 8 image rows x 16 columns of one image (2 tiles per
+  //           image), K block = one filter tap x one 128-byte channel block of the A tensor.  conv_sign -1 walks the taps
+  //           mirrored (dx[p] = sum dy[p - off] W[tap]^T).  Rows are stored at their NHWC position; pad rows are dropped.
+  //   CONV 2 (wgrad): GEMM K = pixels.  K block = conv_rpb image rows x 16 columns of one image; A column (tap, ci) is the
+  //           activation tensor moved by the tap, B is the output-gradient tensor, both MN-major.
+  int conv_c;                          // channels of the tensor behind A
+  int conv_cpb;                        // CONV 1: K blocks per tap (= conv_c / elements per 128-byte row)
+  int conv_sign;                       // CONV 1: +1 fprop, -1 dgrad
+  int conv_rpb, conv_kpi;              // CONV 2: image rows per K block, K blocks per image
+  int conv_brow;                       // CONV 1 with a K-major B (dgrad): rows of B per tap (= channels of the output)
+  int tiles_m;                         // grid.x when it is not ceil(M / 128) (CONV 1: two tiles per image)
+  int ext_reduce;                      // split-K: only write the partial tiles; splitk_reduce_kernel sums them afterwards
   int stages;                          // smem ring depth actually used (<= Cfg::kStages): short-K problems take
                                        // fewer so that several CTAs fit on one SM and their epilogues overlap
 };
@@ -167,7 +182,7 @@ __device__ __forceinline__ void rs_store_staged(const GemmParams& p, const float
 // TF32 = true: fp32 operands in shared memory, kind::tf32 MMAs (K = 8 per instruction).  A 128-byte swizzle row
 // then holds 32 elements instead of 64, so a stage covers 32 K and an MN-major atom is 32 elements wide; the
 // byte geometry (16 KB of A per stage, 32 bytes of K per MMA in K-major form) is the same as for bf16.
-template <int BN, bool A_MN, bool B_MN, bool TF32 = false>
+template <int BN, bool A_MN, bool B_MN, bool TF32 = false, int CONV = 0>
 __global__ void __launch_bounds__(kThreads, TF32 ? 2 : 1)      // fp32 path: two CTAs per SM when the smem ring is short
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const GemmParams p) {
@@ -214,6 +229,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         const int kc = (kb0 + i) * kBKe;
         uint8_t* a = sA + s * C::kABytes;
         uint8_t* b = sB + s * C::kBBytes;
+        if (CONV == 1) {
+          // A tile: 8 image rows x 16 columns of image tile_m / 2, moved by the tap; one 128-byte channel block
+          const int kb = kb0 + i, tap = kb / p.conv_cpb, cb = kb - tap * p.conv_cpb;
+          const int dh = p.conv_sign * (tap / 5 - 2), dw = p.conv_sign * (tap % 5 - 2);
+          tma_load_4d(a, &tma_a, &full_bar[s], cb * kBKe, dw, (tile_m & 1) * 8 + dh, tile_m >> 1);
+          if (!B_MN) {                 // dgrad: B[n = ci][k = co] of this tap
+            tma_load_2d(b, &tma_b, &full_bar[s], cb * kBKe, tap * p.conv_brow + tile_n * BN);
+          } else {                     // fprop: rows (tap, ci) of the filter are the GEMM's K index as they are
+#pragma unroll
+            for (int h = 0; h < BN / kBlkE; ++h)
+              tma_load_2d(b + h * kBlkBytes, &tma_b, &full_bar[s], tile_n * BN + h * kBlkE, kc);
+          }
+          continue;
+        }
+        if (CONV == 2) {
+          const int kb = kb0 + i, img = kb / p.conv_kpi, h0 = (kb - img * p.conv_kpi) * p.conv_rpb;
+#pragma unroll
+          for (int h = 0; h < BM / kBlkE; ++h) {
+            const int col = tile_m * BM + h * kBlkE, tap = col / p.conv_c, c0 = col - tap * p.conv_c;
+            // columns past the 25th tap: a box that lies outside the tensor lands as zeros (and counts its bytes)
+            if (tap < 25) tma_load_4d(a + h * kBlkBytes, &tma_a, &full_bar[s], c0, tap % 5 - 2, h0 + tap / 5 - 2, img);
+            else tma_load_4d(a + h * kBlkBytes, &tma_a, &full_bar[s], 0, 0, 64, img);
+          }
+#pragma unroll
+          for (int h = 0; h < BN / kBlkE; ++h)
+            tma_load_4d(b + h * kBlkBytes, &tma_b, &full_bar[s], tile_n * BN + h * kBlkE, 0, h0, img);
+          continue;
+        }
         if (!A_MN) {
           tma_load_2d(a, &tma_a, &full_bar[s], kc, tile_m * BM);
         } else {
@@ -271,7 +314,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   } else {
     const int q = warp & 3;              // TMEM lane quadrant this warp may read
     const int row = q * 32 + lane;
-    const int grow = tile_m * BM + row;
+    int grow = tile_m * BM + row;
+    if (CONV == 1) {                     // tile row -> NHWC pixel of image tile_m / 2; pad rows / columns are dropped
+      const int hh = (tile_m & 1) * 8 + (row >> 4), ww = row & 15;
+      grow = (hh < 14 && ww < 14) ? (tile_m >> 1) * 196 + hh * 14 + ww : p.M;
+    }
     const unsigned long long step = p.step_ptr ? (unsigned long long)*p.step_ptr : 0ull;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
@@ -311,8 +358,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (warp == 2 && lane == 0) {
-        unsigned old = atomicAdd(&p.counters[tile_id], 1u);
-        *last_flag = (old == (unsigned)(p.splits - 1)) ? 1 : 0;
+        if (p.ext_reduce) {
+          *last_flag = 0;
+        } else {
+          unsigned old = atomicAdd(&p.counters[tile_id], 1u);
+          *last_flag = (old == (unsigned)(p.splits - 1)) ? 1 : 0;
+        }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*last_flag) {
@@ -373,9 +424,9 @@ bool get_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, u
   return true;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool TF32 = false>
+template <int BN, bool A_MN, bool B_MN, bool TF32 = false, int CONV = 0>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, TF32>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, TF32, CONV>;
   // the opt-in to more than 48 KB of dynamic shared memory is a per-device property of the function
   static bool attr_set[64] = {};
   int dev = 0;
@@ -384,10 +435,13 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
     MTB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  dim3 grid((unsigned)mtb::ceil_div(p.M, BM), (unsigned)mtb::ceil_div(p.N, BN), (unsigned)p.splits);
+  dim3 grid((unsigned)(CONV == 1 ? p.tiles_m : mtb::ceil_div(p.M, BM)), (unsigned)mtb::ceil_div(p.N, BN),
+            (unsigned)p.splits);
   GemmParams q = p;
   q.stages = Cfg<BN>::kStages;
   if (TF32 && p.kb_per_split < q.stages) q.stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
+  // implicit convolution at small batch: a 3-deep ring lets two CTAs share an SM, so all tiles are resident at once
+  if (TF32 && CONV == 1 && BN <= 128 && q.stages > 3) q.stages = 3;
   const size_t smem = 1024 + (size_t)q.stages * (Cfg<BN>::kABytes + Cfg<BN>::kBBytes) + 256;
   MTB_CUDA_CHECK(mtb::launch(kern, grid, dim3(kThreads), smem, st, ma, mb, q));
   return 0;
@@ -415,7 +469,7 @@ int mtb_gemm_bf16_rs(const void* A, const void* B, int M, int N, int K, int a_mn
   MTB_REQUIRE(rs->base % 4 == 0 && rs->per > 0 && rs->per % 4 == 0 && ldc % 4 == 0,
               "gemm_rs: base, slice size and ldc must be multiples of 4 elements");
   MTB_REQUIRE((rs->base + (long long)(M - 1) * ldc + N - 1) / rs->per < rs->world, "gemm_rs: output exceeds the slices");
-  GemmParams p;
+  GemmParams p = {};
   p.M = M; p.N = N; p.K = K;
   p.kb_total = (int)mtb::ceil_div(K, BK);
   p.kb_per_split = p.kb_total;
@@ -463,7 +517,7 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: operands must be 16-byte aligned");
   if (bn != 64 && bn != 128 && bn != 256) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
   if (splits < 1) splits = 1;
-  GemmParams p;
+  GemmParams p = {};
   p.M = M; p.N = N; p.K = K;
   p.kb_total = (int)mtb::ceil_div(K, BK);
   if (splits > p.kb_total) splits = p.kb_total;
@@ -508,7 +562,7 @@ int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int 
   if (bn != 64 && bn != 128 && bn != 256) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
   if (splits < 1) splits = 1;
   constexpr int kBKe = 32;
-  GemmParams p;
+  GemmParams p = {};
   p.M = M; p.N = N; p.K = K;
   p.kb_total = (int)mtb::ceil_div(K, kBKe);
   if (splits > p.kb_total) splits = p.kb_total;
@@ -538,6 +592,139 @@ int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int 
   MTB_GEMM_CASE(256, true, true)
 #undef MTB_GEMM_CASE
   return mtb_set_error_msg(MTB_E_ARG, "gemm_tf32: no kernel variant", __FILE__, __LINE__);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// 5x5 SAME convolution on 14x14 maps as an implicit GEMM through the engine above (CONV producer): any channel counts
+// that are multiples of one 128-byte row (32 fp32 / 64 bf16 elements), bf16 or fp32 (TF32 math) tensors.  This is the
+// path of every configuration the specialised 32 -> 64 bf16 shift-GEMM kernels (conv2_sm100.cu) do not cover: the fp32
+// configuration and the widened model.  No im2col / col2im matrix exists anywhere.
+namespace {
+
+// Split-K partial tiles [tile][split][128][bn] summed in split order (deterministic) into out[M][ldc]: one thread per
+// float4 of the result, so a reduction over 21 splits is a 21-deep chain in 12,800 threads instead of in 128.
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, int M, int N, int bn, int splits,
+                                     int tiles_n, long long ldc) {
+  mtb::pdl_sync();
+  const int n4 = N >> 2;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)M * n4) return;
+  const int row = (int)(idx / n4), col = (int)(idx - (long long)row * n4) * 4;
+  const int tile_id = (row / BM) * tiles_n + col / bn;
+  const float* src = ws + ((size_t)tile_id * splits * BM + (row % BM)) * bn + (col % bn);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int s = 0; s < splits; ++s) {
+    const float4 t = __ldcg(reinterpret_cast<const float4*>(src + (size_t)s * BM * bn));
+    acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+  }
+  *reinterpret_cast<float4*>(out + (long long)row * ldc + col) = acc;
+}
+
+struct Map4Key {
+  const void* base; uint64_t c, b; uint32_t box_c, box_rows; int elem_bytes; bool atom32;
+  bool operator<(const Map4Key& o) const {
+    return std::tie(base, c, b, box_c, box_rows, elem_bytes, atom32) <
+           std::tie(o.base, o.c, o.b, o.box_c, o.box_rows, o.elem_bytes, o.atom32);
+  }
+};
+std::map<Map4Key, CUtensorMap> g_maps4;
+
+// NHWC [B,14,14,C] tensor, box = box_c channels x 16 columns x box_rows rows x 1 image
+bool get_map4(CUtensorMap* out, const void* base, uint64_t C, uint64_t B, uint32_t box_c, uint32_t box_rows, int elem_bytes,
+              bool atom32) {
+  std::lock_guard<std::mutex> lk(g_maps_mu);
+  Map4Key k{base, C, B, box_c, box_rows, elem_bytes, atom32};
+  auto it = g_maps4.find(k);
+  if (it != g_maps4.end()) { *out = it->second; return true; }
+  const uint64_t dims[4] = {C, 14, 14, B};
+  const uint64_t strides[3] = {C * elem_bytes, 14 * C * elem_bytes, 196 * C * elem_bytes};
+  const uint32_t box[4] = {box_c, 16, box_rows, 1};
+  const CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const CUtensorMapSwizzle swz = atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUtensorMap m;
+  if (!tma::make(&m, dt, 4, base, dims, strides, box, swz)) return false;
+  if (g_maps4.size() > 1024) g_maps4.clear();
+  g_maps4[k] = m;
+  *out = m;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+// mode 0 fprop : out[B,14,14,Cout] = conv5x5(x[B,14,14,Cin], w[5,5,Cin,Cout]) (+ bias, ReLU)      (mpipy.py:159-160)
+// mode 1 dgrad : out[B,14,14,Cin]  = conv5x5 transposed of dy[B,14,14,Cout] with w                 (Conv2DBackpropInput)
+// mode 2 wgrad : out[5,5,Cin,Cout] (fp32) = sum over pixels of x moved by the tap (x) dy            (Conv2DBackpropFilter)
+//                `x` is the layer input, `w` is dy; split-K over the batch with `workspace` / `counters` as mtb_gemm_bf16.
+// tf32 = 1: every tensor fp32, TF32 tensor-core math; else bf16 tensors (wgrad output always fp32).
+int mtb_conv5x5_gemm(int mode, const void* x, const void* w, void* out, int B, int Cin, int Cout, int tf32,
+                     const float* bias, int relu, int splits, void* workspace, void* counters, cudaStream_t stream) {
+  MTB_REQUIRE(x && w && out && B > 0, "conv5x5_gemm: null pointer or empty batch");
+  MTB_REQUIRE(mode >= 0 && mode <= 2, "conv5x5_gemm: mode must be 0 (fprop), 1 (dgrad) or 2 (wgrad)");
+  const int es = tf32 ? 4 : 2, row_e = 128 / es;                  // elements per 128-byte row
+  MTB_REQUIRE(Cin % row_e == 0 && Cout % row_e == 0, "conv5x5_gemm: channel counts must be multiples of one 128-byte row");
+  GemmParams p = {};
+  p.out_bf16 = tf32 ? 0 : 1; p.bias = nullptr; p.relu = 0; p.keep_prob = 1.0f; p.splits = 1;
+  p.out = out;
+  CUtensorMap ma, mb;
+  if (mode == 0 || mode == 1) {
+    const int Ca = mode == 0 ? Cin : Cout;                        // channels of the tensor behind A
+    const int Nn = mode == 0 ? Cout : Cin;
+    const int bn = Nn % 256 == 0 ? 256 : (Nn % 128 == 0 ? 128 : 64);
+    MTB_REQUIRE(Nn <= 64 || Nn % bn == 0, "conv5x5_gemm: output channels must be <= 64 or a multiple of 128");
+    p.M = B * 196; p.N = Nn; p.K = 25 * Ca; p.ldc = Nn;
+    p.conv_c = Ca; p.conv_cpb = Ca / row_e; p.conv_sign = mode == 0 ? 1 : -1; p.conv_brow = Cin;
+    p.kb_total = 25 * p.conv_cpb; p.kb_per_split = p.kb_total; p.tiles_m = 2 * B;
+    if (mode == 0) { p.bias = bias; p.relu = relu; }
+    MTB_REQUIRE(get_map4(&ma, x, (uint64_t)Ca, (uint64_t)B, (uint32_t)row_e, 8, es, false), "conv5x5_gemm: tensor map for A failed");
+    bool ok;
+    // the filter as a matrix: [25*Cin rows (tap, ci)][Cout]; fprop reads it MN-major (K = rows), dgrad K-major (K = columns)
+    if (mode == 0) ok = tf32 ? get_map(&mb, w, 25ull * Cin, (uint64_t)Cout, (uint64_t)Cout * 4, 32, 32, 4, true)
+                             : get_map(&mb, w, 25ull * Cin, (uint64_t)Cout, (uint64_t)Cout * 2, 64, 64);
+    else ok = tf32 ? get_map(&mb, w, 25ull * Cin, (uint64_t)Cout, (uint64_t)Cout * 4, (uint32_t)bn, 32, 4)
+                   : get_map(&mb, w, 25ull * Cin, (uint64_t)Cout, (uint64_t)Cout * 2, (uint32_t)bn, 64);
+    MTB_REQUIRE(ok, "conv5x5_gemm: tensor map for the filter failed");
+#define MTB_CONV_CASE(BN_, BMN_, TF_) if (bn == BN_ && (mode == 0) == BMN_ && (tf32 != 0) == TF_) return launch<BN_, false, BMN_, TF_, 1>(ma, mb, p, stream);
+    MTB_CONV_CASE(64, true, true) MTB_CONV_CASE(64, false, true) MTB_CONV_CASE(128, true, true) MTB_CONV_CASE(128, false, true)
+    MTB_CONV_CASE(256, true, true) MTB_CONV_CASE(256, false, true)
+    MTB_CONV_CASE(64, true, false) MTB_CONV_CASE(64, false, false) MTB_CONV_CASE(128, true, false) MTB_CONV_CASE(128, false, false)
+    MTB_CONV_CASE(256, true, false) MTB_CONV_CASE(256, false, false)
+#undef MTB_CONV_CASE
+    return mtb_set_error_msg(MTB_E_ARG, "conv5x5_gemm: no kernel variant", __FILE__, __LINE__);
+  }
+  // wgrad: M = (tap, ci), N = co, K = pixels walked as (image, rows-of-16)
+  const int bn = Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : 64);
+  MTB_REQUIRE(Cout <= 64 || Cout % bn == 0, "conv5x5_gemm: output channels must be <= 64 or a multiple of 128");
+  const int kbe = tf32 ? 32 : 64;                                  // K rows (pixels) per block
+  p.M = 25 * Cin; p.N = Cout; p.ldc = Cout; p.out_bf16 = 0;
+  p.conv_c = Cin; p.conv_rpb = kbe / 16; p.conv_kpi = (14 + p.conv_rpb - 1) / p.conv_rpb;
+  p.kb_total = B * p.conv_kpi; p.K = p.kb_total * kbe;
+  if (splits < 1) splits = 1;
+  if (splits > p.kb_total) splits = p.kb_total;
+  p.kb_per_split = (int)mtb::ceil_div(p.kb_total, splits);
+  p.splits = (int)mtb::ceil_div(p.kb_total, p.kb_per_split);
+  MTB_REQUIRE(p.splits == 1 || (workspace && counters), "conv5x5_gemm: split-K needs workspace and counters");
+  p.workspace = reinterpret_cast<float*>(workspace);
+  p.counters = reinterpret_cast<unsigned int*>(counters);
+  MTB_REQUIRE(get_map4(&ma, x, (uint64_t)Cin, (uint64_t)B, (uint32_t)row_e, (uint32_t)p.conv_rpb, es, tf32 != 0),
+              "conv5x5_gemm: tensor map for the activations failed");
+  MTB_REQUIRE(get_map4(&mb, w, (uint64_t)Cout, (uint64_t)B, (uint32_t)row_e, (uint32_t)p.conv_rpb, es, tf32 != 0),
+              "conv5x5_gemm: tensor map for the output gradient failed");
+  p.ext_reduce = p.splits > 1 ? 1 : 0;                  // partial tiles summed by a wide second launch, not by the last CTA
+  int rc = MTB_E_ARG;
+#define MTB_CONV_CASE(BN_, TF_) if (bn == BN_ && (tf32 != 0) == TF_) rc = launch<BN_, true, true, TF_, 2>(ma, mb, p, stream);
+  MTB_CONV_CASE(64, true) MTB_CONV_CASE(128, true) MTB_CONV_CASE(256, true)
+  MTB_CONV_CASE(64, false) MTB_CONV_CASE(128, false) MTB_CONV_CASE(256, false)
+#undef MTB_CONV_CASE
+  if (rc != 0 || !p.ext_reduce) return rc;
+  const long long n_vec = (long long)p.M * (p.N / 4);
+  MTB_CUDA_CHECK(mtb::launch(splitk_reduce_kernel, dim3((unsigned)((n_vec + 255) / 256)), dim3(256), 0, stream,
+                             (const float*)p.workspace, reinterpret_cast<float*>(out), p.M, p.N, bn, p.splits,
+                             (int)mtb::ceil_div(p.N, bn), p.ldc));
+  return 0;
 }
 
 }  // extern "C"
@@ -610,7 +797,7 @@ int mtb_gemm_bf16_splitk_noalloc(const void* A, const void* B, void* out, int M,
   if (bn == 0) bn = 64;                                  // 0 = default tile width
   MTB_REQUIRE(bn == 64 || bn == 128, "gemm_noalloc: bn must be 0 (default), 64 or 128");
   if (splits < 1) splits = 1;
-  GemmParams p;
+  GemmParams p = {};
   p.M = M; p.N = N; p.K = K;
   p.kb_total = (int)mtb::ceil_div(K, BK);
   if (splits > p.kb_total) splits = p.kb_total;

@@ -66,6 +66,15 @@ int mtb_gemm_tf32(const float* A, const float* B, float* out, int M, int N, int 
                   unsigned long long seed, const long long* step_ptr, int bn, int splits, void* workspace,
                   void* counters, cudaStream_t stream);
 
+/* 5x5 SAME convolution on 14x14 maps as an implicit GEMM on the same engine (tf.nn.conv2d mpipy.py:159 and its two
+ * gradients): the producer addresses the NHWC tensor through a 4-D TMA map, no im2col / col2im matrix is ever built.
+ * Any channel counts that are multiples of one 128-byte row (32 fp32 / 64 bf16); tf32 != 0: fp32 tensors, TF32 math.
+ * mode 0 fprop (x, w[5,5,Cin,Cout]) -> out[B,14,14,Cout] (+ bias, ReLU); mode 1 dgrad (x = dy, w) -> out[B,14,14,Cin];
+ * mode 2 wgrad (x = layer input, w = dy) -> out[5,5,Cin,Cout] fp32, split-K over the batch (workspace / counters sized
+ * with mtb_gemm_workspace_bytes(25*Cin, Cout, bn, splits) / mtb_gemm_counter_bytes, bn = 256 / 128 / 64 by Cout). */
+int mtb_conv5x5_gemm(int mode, const void* x, const void* w, void* out, int B, int Cin, int Cout, int tf32,
+                     const float* bias, int relu, int splits, void* workspace, void* counters, cudaStream_t stream);
+
 /* Split-K GEMM with built-in scratch, for callers that cannot allocate or pass device scratch (a plug-in inside a
  * process whose allocator owns the whole GPU, an allocation-free control loop, a bare C caller without a tensor
  * library).  No counterpart in the reference.  Same product/epilogue as mtb_gemm_bf16 (bias, ReLU, bf16/fp32

@@ -211,18 +211,32 @@ class NativeEngine:
         # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
         want = self.conv_impl
         have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2)) and not self.fp32
-        if want == "implicit" and not have:
-            raise ValueError(f"no implicit-GEMM conv2 kernel for {s.c1}->{s.c2} channels")
         self.conv2_implicit = have and want != "im2col"
+        # every other shape whose channel counts fill whole 128-byte rows: implicit GEMM through the GEMM engine's
+        # convolution producer (4-D TMA over the NHWC tensor), still no im2col.  What is left for im2col + GEMM is
+        # conv_impl="im2col" (kept as a second implementation for the tests) and odd channel counts.
+        row_e = 32 if self.fp32 else 64
+        self.conv2_igemm = (not self.conv2_implicit and want != "im2col" and s.c1 % row_e == 0 and s.c2 % row_e == 0
+                            and (s.c2 <= 64 or s.c2 % 128 == 0) and (s.c1 <= 64 or s.c1 % 128 == 0))
+        if want == "implicit" and not (have or self.conv2_igemm):
+            raise ValueError(f"no implicit-GEMM conv2 kernel for {s.c1}->{s.c2} channels")
         if self.conv2_implicit:
             self.c2_ws = torch.zeros(N.lib().mtb_conv2_wgrad_workspace_bytes(Bmax), dtype=torch.uint8, device=dev)
         else:
-            self.col = z(Bmax * 196, 25 * s.c1)
             self.a2 = z(Bmax * 196, s.c2)
-            self.dcol = z(Bmax * 196, 25 * s.c1)
+            bn = 256 if s.c2 % 256 == 0 else (128 if s.c2 % 128 == 0 else 64)
+            if self.conv2_igemm:
+                # split-K over the batch so that the weight gradient covers the chip
+                tiles = -(-25 * s.c1 // 128) * -(-s.c2 // bn)
+                kb_total = self.B * (7 if self.fp32 else 4)
+                self.wg_splits = max(1, min(kb_total, 148 // tiles))
+            else:
+                self.col = z(Bmax * 196, 25 * s.c1)
+                self.dcol = z(Bmax * 196, 25 * s.c1)
+                bn = 64
+                self.wg_splits = 16        # 21 splits (one full wave at 32->64 channels) measured slower: 43.7 vs 38.2 us
             # split-K scratch for the conv2 weight gradient (K = B*196 is the long axis)
-            self.wg_splits = 16            # 21 splits (one full wave at 32->64 channels) measured slower: 43.7 vs 38.2 us
-            ws, cn = N.gemm_scratch_sizes(25 * s.c1, s.c2, 64, self.wg_splits)
+            ws, cn = N.gemm_scratch_sizes(25 * s.c1, s.c2, bn, self.wg_splits)
             self.wg_ws = torch.zeros(max(ws, 16), dtype=torch.uint8, device=dev)
             self.wg_cnt = torch.zeros(max(cn, 16), dtype=torch.uint8, device=dev)
 
@@ -400,6 +414,11 @@ class NativeEngine:
         if self.conv2_implicit:
             N.call("mtb_conv2_fprop_pool", self.a1p.data_ptr(), S["conv2_weight"].data_ptr(),
                    P["conv2_bias"].data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B)
+        elif self.conv2_igemm:
+            N.call("mtb_conv5x5_gemm", 0, self.a1p.data_ptr(), S["conv2_weight"].data_ptr(), self.a2.data_ptr(), B, s.c1,
+                   s.c2, int(self.fp32), P["conv2_bias"].data_ptr(), 1, 1, None, None)
+            N.call("mtb_maxpool2x2_fwd" + sfx, self.a2.data_ptr(), self.a2p.data_ptr(), self.idx2.data_ptr(), B, 14, 14,
+                   s.c2)
         else:
             N.call("mtb_im2col_5x5" + sfx, self.a1p.data_ptr(), self.col.data_ptr(), B, 14, 14, s.c1)
             gemm(self.col, S["conv2_weight"].view(K2, s.c2), self.a2, M2, s.c2, K2, False, True,
@@ -498,14 +517,23 @@ class NativeEngine:
                    self.da2.data_ptr(), B, 14, 14, s.c2)
             da2 = self.da2.view(self.Bmax * 196, s.c2)
             N.call("mtb_colsum_f32" if self.fp32 else "mtb_colsum_bf16", da2.data_ptr(), G["conv2_bias"].data_ptr(), M2, s.c2)
-            # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
-            gemm(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
-                 splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
-            if after_conv2_wgrad is not None:
-                after_conv2_wgrad()
-            # conv2 dgrad: dcol = da2 W2^T, then col2im
-            gemm(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
-            N.call("mtb_col2im_5x5" + sfx, self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
+            if self.conv2_igemm:
+                # wgrad and dgrad as implicit GEMMs straight from the NHWC tensors (split-K over the batch for wgrad)
+                N.call("mtb_conv5x5_gemm", 2, self.a1p.data_ptr(), da2.data_ptr(), G["conv2_weight"].data_ptr(), B, s.c1,
+                       s.c2, int(self.fp32), None, 0, self.wg_splits, self.wg_ws.data_ptr(), self.wg_cnt.data_ptr())
+                if after_conv2_wgrad is not None:
+                    after_conv2_wgrad()
+                N.call("mtb_conv5x5_gemm", 1, da2.data_ptr(), S["conv2_weight"].data_ptr(), self.dp1.data_ptr(), B, s.c1,
+                       s.c2, int(self.fp32), None, 0, 1, None, None)
+            else:
+                # conv2 wgrad: dW = col^T da2, K = B*196 -> split-K with last-arriver reduction
+                gemm(self.col, da2, G["conv2_weight"].view(K2, s.c2), K2, s.c2, M2, True, True, bn=64,
+                     splits=self.wg_splits, workspace=self.wg_ws, counters=self.wg_cnt)
+                if after_conv2_wgrad is not None:
+                    after_conv2_wgrad()
+                # conv2 dgrad: dcol = da2 W2^T, then col2im
+                gemm(da2, S["conv2_weight"].view(K2, s.c2), self.dcol, M2, K2, s.c2, False, False, bn=128)
+                N.call("mtb_col2im_5x5" + sfx, self.dcol.data_ptr(), self.dp1.data_ptr(), B, 14, 14, s.c1)
         # pool1 + ReLU backward fused into the conv1 weight gradient
         if self.conv1_tc:
             wx, _, wstep, wrows = self._win()

@@ -61,6 +61,7 @@ _SIGS = {
                       vp, vp, vp],
     "mtb_gemm_bf16_rs": [vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, C.POINTER(GemmRS), vp],
     "mtb_gemm_tf32": [vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, vp, i32, f32, u64, vp, i32, i32, vp, vp, vp],
+    "mtb_conv5x5_gemm": [i32, vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, vp, vp, vp],
     "mtb_conv1_fwd_f32": [vp, vp, vp, vp, vp, i32, i32, vp],
     "mtb_conv1_wgrad_f32": [vp, vp, vp, vp, vp, vp, i32, i32, vp],
     "mtb_maxpool2x2_fwd_f32": [vp, vp, vp, i32, i32, i32, i32, vp],
@@ -165,12 +166,15 @@ def stream_ptr() -> int:
 
 
 _KERNELS_PER_CALL = {"mtb_conv2_wgrad": 2, "mtb_conv2_wgrad_unpool": 2}      # main kernel + partial-sum reduction
+# (mtb_conv5x5_gemm in wgrad mode with splits > 1 also launches two; `call` counts it below)
 
 
 def call(name: str, *args) -> None:
     """Call ``name(*args, current_stream)`` and raise on a non-zero return."""
     global LAUNCHES
     LAUNCHES += _KERNELS_PER_CALL.get(name, 1)
+    if name == "mtb_conv5x5_gemm" and args[0] == 2 and args[10] > 1:
+        LAUNCHES += 1
     check(getattr(lib(), name)(*args, stream_ptr()), name)
 
 

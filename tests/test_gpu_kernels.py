@@ -389,6 +389,58 @@ def test_conv2_fprop_pool_implicit_gemm(N, dev, B):
     assert int(idx.max()) <= 3
 
 
+# Implicit-GEMM convolution through the GEMM engine's 4-D TMA producer (any channel counts, bf16 or fp32 / TF32):
+# the path of the fp32 configuration and of the widened model.  Reference: the plain fp32 oracle.
+_IGEMM_CASES = [(3, 32, 64, True), (100, 32, 64, True), (2, 64, 128, True), (2, 128, 256, False), (37, 64, 64, False)]
+
+
+def _igemm_scratch(N, dev, cin, cout, splits):
+    bn = 256 if cout % 256 == 0 else (128 if cout % 128 == 0 else 64)
+    ws, cn = N.gemm_scratch_sizes(25 * cin, cout, bn, splits)
+    return (torch.zeros(max(ws, 16), dtype=torch.uint8, device=dev),
+            torch.zeros(max(cn, 16), dtype=torch.uint8, device=dev))
+
+
+@pytest.mark.parametrize("B,cin,cout,tf32", _IGEMM_CASES)
+def test_conv5x5_implicit_gemm_fprop_dgrad_wgrad(N, dev, B, cin, cout, tf32):
+    dt = torch.float32 if tf32 else torch.bfloat16
+    g = torch.Generator().manual_seed(B * 1000 + cin)
+    x = torch.relu(torch.randn(B, 14, 14, cin, generator=g)).to(dt)
+    w = (torch.randn(5, 5, cin, cout, generator=g) * 0.05).to(dt)
+    dy = (torch.randn(B, 14, 14, cout, generator=g) * (torch.rand(B, 14, 14, cout, generator=g) < 0.5)).to(dt)
+    bias = torch.randn(cout, generator=g) * 0.1
+    xd, wd, dyd, bd = x.to(dev), w.to(dev), dy.to(dev), bias.to(dev)
+    tol = 2e-3 if tf32 else 5e-3                  # TF32 operands (10-bit mantissa) / bf16 output rounding
+    # fprop + bias + ReLU
+    out = torch.full((B, 14, 14, cout), float("nan"), dtype=dt, device=dev)
+    N.call("mtb_conv5x5_gemm", 0, xd.data_ptr(), wd.data_ptr(), out.data_ptr(), B, cin, cout, int(tf32), bd.data_ptr(),
+           1, 1, None, None)
+    torch.cuda.synchronize()
+    ref = torch.relu(O.conv5x5(x.float(), w.float()) + bias)
+    assert torch.isfinite(out).all()
+    assert _rel(out.cpu(), ref) < tol
+    # dgrad
+    dx = torch.full((B, 14, 14, cin), float("nan"), dtype=dt, device=dev)
+    N.call("mtb_conv5x5_gemm", 1, dyd.data_ptr(), wd.data_ptr(), dx.data_ptr(), B, cin, cout, int(tf32), None, 0, 1,
+           None, None)
+    torch.cuda.synchronize()
+    ref = O.conv5x5_dgrad(dy.float(), w.float(), (B, 14, 14, cin))
+    assert torch.isfinite(dx).all()
+    assert _rel(dx.cpu(), ref) < tol
+    # wgrad, split-K over the batch, twice (self-cleaning tile counters)
+    splits = max(1, min(B, 5))
+    ws, cnt = _igemm_scratch(N, dev, cin, cout, splits)
+    dW = torch.full((5, 5, cin, cout), float("nan"), device=dev)
+    ref = O.conv5x5_wgrad(x.float(), dy.float()).reshape(5, 5, cin, cout)
+    for rep in range(2):
+        N.call("mtb_conv5x5_gemm", 2, xd.data_ptr(), dyd.data_ptr(), dW.data_ptr(), B, cin, cout, int(tf32), None, 0,
+               splits, ws.data_ptr(), cnt.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.isfinite(dW).all(), rep
+        assert _rel(dW.cpu(), ref) < tol, rep
+        dW.fill_(float("nan"))
+
+
 @pytest.mark.parametrize("B", [1, 5, 149, 300])
 def test_conv2_dgrad_implicit_gemm(N, dev, B):
     dy = _bf(torch.randn(B, 14, 14, 64)).to(dev)
