@@ -59,6 +59,9 @@ def parse():
     ap.add_argument("--overlap", action="store_true", help="(default with peers) bucketed K1: fc bucket hidden under the conv backward")
     ap.add_argument("--no-overlap", action="store_true", help="one whole-buffer K1 launch at the end of the step")
     ap.add_argument("--comm-dtype", default="fp32", choices=["fp32", "bf16"], help="gradient wire format")
+    ap.add_argument("--reference-semantics", action="store_true",
+                    help="time the reference's own schedule (tutorial CNN, batch 64, fp32, root-only weight average every "
+                         "50 steps, full test-shard eval every step): --impl ours | baseline (literal library restatement)")
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--fuse-wgrad-rs", action="store_true",
                     help="FC1 weight gradient: GEMM -> reduce-scatter in one kernel over peer memory (N > 1)")
@@ -288,6 +291,16 @@ def run_baseline(args) -> dict:
 
 def main():
     args = parse()
+    if args.reference_semantics and args.impl in ("ours", "baseline"):
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import reference_semantics as RS
+        out = (RS.run_ours if args.impl == "ours" else RS.run_baseline)(args.steps, max(args.warmup, 3))
+        if out:
+            print(json.dumps({"metric": "reference_semantics_images_per_sec", **out}), flush=True)
+        if args.impl == "baseline" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            sys.stdout.flush()
+            os._exit(0)
+        return 0
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) == 0:
             print(json.dumps(run_reference(args)), flush=True)
