@@ -182,12 +182,14 @@ __device__ __forceinline__ void rs_store_staged(const GemmParams& p, const float
 // TF32 = true: fp32 operands in shared memory, kind::tf32 MMAs (K = 8 per instruction).  A 128-byte swizzle row
 // then holds 32 elements instead of 64, so a stage covers 32 K and an MN-major atom is 32 elements wide; the
 // byte geometry (16 KB of A per stage, 32 bytes of K per MMA in K-major form) is the same as for bf16.
-template <int BN, bool A_MN, bool B_MN, bool TF32 = false, int CONV = 0>
-__global__ void __launch_bounds__(kThreads, TF32 ? 2 : 1)      // fp32 path: two CTAs per SM when the smem ring is short
+// TWO: built for two CTAs per SM (168 registers, ring depth chosen at launch): one CTA's epilogue runs under the other's
+// main loop, and a grid of up to 296 tiles is a single wave.
+template <int BN, bool A_MN, bool B_MN, bool TF32 = false, int CONV = 0, bool TWO = false>
+__global__ void __launch_bounds__(kThreads, (TF32 || TWO) ? 2 : 1)      // fp32 path: two CTAs per SM when the smem ring is short
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const GemmParams p) {
   using C = Cfg<BN>;
-  const int S = TF32 ? p.stages : C::kStages;        // compile-time for the bf16 instantiations
+  const int S = (TF32 || TWO) ? p.stages : C::kStages;        // compile-time for the one-CTA-per-SM bf16 instantiations
   constexpr int kBKe = TF32 ? 32 : 64;             // K elements per stage (one 128-byte row)
   constexpr int kBlkE = TF32 ? 32 : 64;            // MN elements per MN-major atom column
   constexpr int kBlkBytes = kBKe * 128;            // one MN-major block: kBKe K-rows of 128 bytes
@@ -424,9 +426,9 @@ bool get_map(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, u
   return true;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool TF32 = false, int CONV = 0>
+template <int BN, bool A_MN, bool B_MN, bool TF32 = false, int CONV = 0, bool TWO = false>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, TF32, CONV>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, TF32, CONV, TWO>;
   // the opt-in to more than 48 KB of dynamic shared memory is a per-device property of the function
   static bool attr_set[64] = {};
   int dev = 0;
@@ -442,6 +444,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
   if (TF32 && p.kb_per_split < q.stages) q.stages = p.kb_per_split < 2 ? 2 : p.kb_per_split;
   // implicit convolution at small batch: a 3-deep ring lets two CTAs share an SM, so all tiles are resident at once
   if (TF32 && CONV == 1 && BN <= 128 && q.stages > 3) q.stages = 3;
+  if (TWO) q.stages = 3;                                 // 3 x 32 KB (BN 128): two CTAs fit in the 227 KB of an SM
   const size_t smem = 1024 + (size_t)q.stages * (Cfg<BN>::kABytes + Cfg<BN>::kBBytes) + 256;
   MTB_CUDA_CHECK(mtb::launch(kern, grid, dim3(kThreads), smem, st, ma, mb, q));
   return 0;
@@ -515,6 +518,8 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   MTB_REQUIRE(A && B && out && M > 0 && N > 0 && K > 0, "gemm: null pointer or empty shape");
   MTB_REQUIRE((lda * 2) % 16 == 0 && (ldb * 2) % 16 == 0, "gemm: operand row pitch must be a multiple of 16 bytes");
   MTB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: operands must be 16-byte aligned");
+  const bool two = bn == 129 && a_mn_major == b_mn_major && splits <= 1;      // BN 128, two CTAs per SM
+  if (bn == 129) bn = 128;
   if (bn != 64 && bn != 128 && bn != 256) bn = (N % 128 == 0 && mtb::ceil_div(M, BM) * (N / 128) >= 96) ? 128 : 64;
   if (splits < 1) splits = 1;
   GemmParams p = {};
@@ -538,6 +543,9 @@ int mtb_gemm_bf16(const void* A, const void* B, void* out, int M, int N, int K, 
   ok = b_mn_major ? get_map(&mb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, 64, 64)
                   : get_map(&mb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, (uint32_t)bn, 64);
   MTB_REQUIRE(ok, "gemm: cuTensorMapEncodeTiled failed for B");
+  // bn = 129: BN 128 tiles built for two CTAs per SM (dgrad / wgrad forms only)
+  if (two && !a_mn_major) return launch<128, false, false, false, 0, true>(ma, mb, p, stream);
+  if (two && a_mn_major) return launch<128, true, true, false, 0, true>(ma, mb, p, stream);
 #define MTB_GEMM_CASE(BN_, AM_, BM_)                                            \
   if (bn == BN_ && (a_mn_major != 0) == AM_ && (b_mn_major != 0) == BM_) return launch<BN_, AM_, BM_>(ma, mb, p, stream);
   MTB_GEMM_CASE(128, false, false) MTB_GEMM_CASE(128, false, true) MTB_GEMM_CASE(128, true, false)

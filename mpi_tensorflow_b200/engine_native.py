@@ -475,8 +475,10 @@ class NativeEngine:
             N.call("mtb_colsum_f32" if self.fp32 else "mtb_colsum_bf16", self.dh.data_ptr(), G["fc1_bias"].data_ptr(), B, s.fc)
         # dflat = dh W1^T : W1 [in,out] row-major is already the K-major B operand.  Runs BEFORE the
         # weight gradient so that the last reader of the FC1 weights is done when the bucket closes.
-        bn = 256 if B >= 512 else 128
-        tiles = -(-B // 128) * -(-s.flat_dim // bn)
+        # bf16 at large batch: 128-wide tiles in the build that puts two CTAs on an SM (bn 129): 200 tiles in one wave, one
+        # CTA's epilogue under the other's main loop: 16.0 us vs 18.7 (256-wide) / 21.3 (128-wide, one per SM); cuBLAS 14.5
+        bn = (129 if not self.fp32 else 256) if B >= 512 else 128
+        tiles = -(-B // 128) * -(-s.flat_dim // min(bn, 256))
         # (split-K measured slower here in both precisions: fp32 batch 100, 4 splits, 25.2 vs 16.1 us)
         splits = max(1, min(4, 128 // tiles)) if (tiles < 64 and os.environ.get("MTB_FC_SPLITK") == "1") else 1
         ws, cnt = self._splitk_scratch("fc1_dgrad", B, s.flat_dim, bn, splits)
@@ -484,11 +486,11 @@ class NativeEngine:
              workspace=ws, counters=cnt)
         # dW1 = flat^T dh : both operands MN-major, fp32 straight into the gradient bucket (K = batch: wide tiles
         # only pay off when K is long enough to amortise their epilogue)
-        wbn = 256 if (s.fc % 256 == 0 and B >= 512) else 128
+        wbn = (129 if not self.fp32 else 256) if (s.fc % 256 == 0 and B >= 512) else 128       # 17.6 vs 19.7 us
         if self._rs_active:
             # ... added tile by tile into the slice owners' buckets over NVLink: the reduce-scatter half of the
             # gradient allreduce happens inside this GEMM, K1 only updates and broadcasts (prered range)
-            N.gemm_bf16_rs(flat, self.dh, s.flat_dim, s.fc, B, True, True, s.fc, wbn, self._rs)
+            N.gemm_bf16_rs(flat, self.dh, s.flat_dim, s.fc, B, True, True, s.fc, 256 if wbn == 129 else wbn, self._rs)
         elif self._lp:
             # bf16 wire format: the epilogue rounds once and K1 reads 2 bytes per element from every peer
             gemm(flat, self.dh, self.Glp["fc1_weight"], s.flat_dim, s.fc, B, True, True, bn=wbn)
@@ -931,14 +933,19 @@ class NativeEngine:
             self._step_body(peers)
 
     # ------------------------------------------------------------------ host-streamed training
+    # Input ring of the host-streamed loop: a batch may be copied up to three steps ahead of the step that reads it.
+    # With two buffers (one step ahead) 8 ranks ran 8 % below their device-resident rate: one late host->device copy
+    # on any rank stalls all of them at the next allreduce; a deeper ring absorbs that jitter.
+    _STREAM_BUFS = 4
+
     def stream_steps(self, hx: torch.Tensor, hy: torch.Tensor, steps: int, ring: int = 4,
                      peers: bool = True) -> List[float]:
         """``steps`` optimizer steps over a dataset that lives in PINNED HOST memory
         (``hx`` [rows, 784] fp32, ``hy`` [rows] int32), walked with the reference's sequential
         window (``mpipy.py:80-82``).  This is the reference's feed loop (``mpipy.py:83-85``: one
         host->device feed per step) done the B200 way: step i+1's batch is copied on a copy
-        stream into the other half of a double buffer while step i computes (one CUDA graph per
-        half, so the kernels read it in place), and each step's loss is mailed by the update
+        stream into the next slot of a small ring of input buffers while step i computes (one CUDA
+        graph per slot, so the kernels read it in place), and each step's loss is mailed by the update
         kernel into a pinned host ring (:meth:`_await_loss`) that the host polls a few steps
         later, so neither transfer ever stalls the GPU.  Returns the loss of every step."""
         B, dev = self.B, self.device
@@ -952,10 +959,10 @@ class NativeEngine:
             raise ValueError("dataset smaller than one batch")
         if self._stream_state is None:
             self._stream_state = dict(
-                x=[torch.empty(B, 784, device=dev) for _ in range(2)],
-                y=[torch.empty(B, dtype=torch.int32, device=dev) for _ in range(2)],
-                ready=[torch.cuda.Event() for _ in range(2)],
-                consumed=[torch.cuda.Event() for _ in range(2)],
+                x=[torch.empty(B, 784, device=dev) for _ in range(self._STREAM_BUFS)],
+                y=[torch.empty(B, dtype=torch.int32, device=dev) for _ in range(self._STREAM_BUFS)],
+                ready=[torch.cuda.Event() for _ in range(self._STREAM_BUFS)],
+                consumed=[torch.cuda.Event() for _ in range(self._STREAM_BUFS)],
                 copy=torch.cuda.Stream(device=dev),
             )
         st = self._stream_state
@@ -968,7 +975,7 @@ class NativeEngine:
         losses: List[float] = []
         first = self.opt_step + 1
         for i in range(steps):
-            k = i & 1
+            k = i % self._STREAM_BUFS
             # the reference's window, on the GLOBAL step so that a resumed or continued run walks on (mpipy.py:80-82)
             o = ((self.opt_step * B) % (rows - B)) if rows > B else 0
             copy.wait_event(st["consumed"][k])                 # the step that used this half has copied it out

@@ -17,7 +17,8 @@ def timeit(fn, iters=50):
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 shapes = [("fc1 fprop", B, 1024, 3136, False, True, 64), ("fc1 fprop bn128", B, 1024, 3136, False, True, 128),
           ("fc1 dgrad", B, 3136, 1024, False, False, 128), ("fc1 dgrad bn256", B, 3136, 1024, False, False, 256),
-          ("fc1 wgrad", 3136, 1024, B, True, True, 128), ("fc1 wgrad bn256", 3136, 1024, B, True, True, 256), ("fc1 fprop bn256", B, 1024, 3136, False, True, 256)]
+          ("fc1 wgrad", 3136, 1024, B, True, True, 128), ("fc1 wgrad bn256", 3136, 1024, B, True, True, 256), ("fc1 fprop bn256", B, 1024, 3136, False, True, 256),
+          ("fc1 dgrad bn128x2", B, 3136, 1024, False, False, 129), ("fc1 wgrad bn128x2", 3136, 1024, B, True, True, 129)]
 for name, M, Nn, K, a_mn, b_mn, bn in shapes:
     A = torch.randn(M, K, device=dev).to(torch.bfloat16)
     Bm = torch.randn(K, Nn, device=dev).to(torch.bfloat16)
