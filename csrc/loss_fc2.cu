@@ -353,12 +353,132 @@ fc2_bwd_fused_kernel(const T* __restrict__ h, const float* __restrict__ dlogits,
   TRACE2(5);
 }
 
+// Same head, 8 rows per block instead of 32: four times as many blocks (128 at batch 1024, 13 at batch 100 - the
+// 32-row form ran on 32 and 4 SMs) and an eighth of the shared-memory reads per block.  Lane = (row r = lane & 7,
+// quarter q = lane >> 3); warp w owns features [w F/16, (w+1) F/16) and each lane a contiguous quarter of them, so a lane
+// loads whole 16-byte vectors of its row.  W rows are stored in shared memory with 8 extra words per 16 feature chunk
+// group so that the four quarters of a warp read four different banks; products are read as float2 (LDS.64).
+template <int NC, class T>
+__global__ void __launch_bounds__(kHeadWarps * 32)
+fc2_softmax_ce_rows8_kernel(const T* __restrict__ h, const float* __restrict__ W /*[F,NC]*/,
+                            const float* __restrict__ bias, const int* __restrict__ labels, float* __restrict__ logits,
+                            float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ loss_accum,
+                            int* __restrict__ err_accum, int B, int F, const long long* win_step, long long win_rows) {
+  static_assert(NC % 2 == 0, "float2 reads of a weight row");
+  extern __shared__ float sm[];
+  pdl_sync();
+  if (labels != nullptr && win_step != nullptr) labels += ((*win_step) * (long long)B) % (win_rows - B);
+  const int chunk = F / (kHeadWarps * 4);              // features per lane
+  // feature f lives at sW[f * NC + (f / chunk) * 8]: consecutive quarters are 8 words apart modulo 32 banks
+  float* sW = sm;
+  float* red = sm + (size_t)F * NC + (F / chunk) * 8;  // [kHeadWarps][8 rows][NC]
+  for (int i = threadIdx.x; i < F * NC / 2; i += blockDim.x) {
+    const int f = (2 * i) / NC;
+    *reinterpret_cast<float2*>(sW + 2 * i + (f / chunk) * 8) = __ldg(reinterpret_cast<const float2*>(W) + i);
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = lane & 7, q = lane >> 3;
+  const int row = blockIdx.x * 8 + r;
+  const int f0 = (warp * 4 + q) * chunk;
+  float acc[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) acc[c] = 0.f;
+  if (row < B) {
+    const T* hr = h + (size_t)row * F + f0;
+    const float* wbase = sW + (size_t)f0 * NC + (f0 / chunk) * 8;
+    for (int i = 0; i < chunk / 8; ++i) {
+      float hv[8];
+      load8f(hr + i * 8, hv);
+      const float2* wr = reinterpret_cast<const float2*>(wbase + (size_t)i * 8 * NC);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+#pragma unroll
+        for (int c = 0; c < NC / 2; ++c) {
+          const float2 w2 = wr[e * (NC / 2) + c];
+          acc[2 * c] = fmaf(hv[e], w2.x, acc[2 * c]);
+          acc[2 * c + 1] = fmaf(hv[e], w2.y, acc[2 * c + 1]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {                       // the four quarters of a row, then the 16 warps through smem
+    acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 8);
+    acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 16);
+  }
+  if (q == 0) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) red[(warp * 8 + r) * NC + c] = acc[c];
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  const bool valid = lane < 8 && row < B;
+  float lg[NC];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    float s = __ldg(bias + c);
+    if (lane < 8) {
+#pragma unroll
+      for (int w = 0; w < kHeadWarps; ++w) s += red[(w * 8 + r) * NC + c];
+    }
+    lg[c] = s;
+    mx = fmaxf(mx, s);
+  }
+  float s = 0.f, e[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) { e[c] = expf(lg[c] - mx); s += e[c]; }
+  const float inv = 1.0f / s, invB = 1.0f / (float)B;
+  const int y = (labels && valid) ? labels[row] : -1;
+  int arg = 0;
+  float best = -INFINITY, ly = 0.f;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    if (lg[c] > best) { best = lg[c]; arg = c; }
+    if (c == y) ly = lg[c];
+  }
+  if (valid) {
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const float p = e[c] * inv;
+      if (logits) logits[(size_t)row * NC + c] = lg[c];
+      if (probs) probs[(size_t)row * NC + c] = p;
+      if (dlogits) dlogits[(size_t)row * NC + c] = (p - (c == y ? 1.f : 0.f)) * invB;
+    }
+  }
+  float l = (valid && y >= 0) ? -(ly - mx - logf(s)) * invB : 0.f;
+  l = warp_sum(l);
+  const unsigned wrong = __ballot_sync(0xffffffffu, valid && y >= 0 && arg != y);
+  if (lane == 0) {
+    if (loss_accum && labels) atomicAdd(loss_accum, l);
+    if (err_accum && wrong) atomicAdd(err_accum, __popc(wrong));
+  }
+}
+
 template <class T>
 int run_head_fast(const T* h, const float* W, const float* bias, const int* labels, float* logits, float* probs,
                   float* dlogits, float* loss_accum, int* err_accum, int B, int F, int NC, const long long* win_step,
                   long long win_rows, cudaStream_t stream) {
   MTB_REQUIRE(NC == 10 && F % (8 * kHeadWarps) == 0, "fc2_softmax_ce_fast: 10 classes, F a multiple of 128");
   MTB_REQUIRE(win_step == nullptr || win_rows > B, "fc2_softmax_ce_fast: shard must be larger than the batch");
+  if (F % (kHeadWarps * 4 * 8) == 0) {                   // every lane owns whole 8-feature vectors: the 8-row form
+    const int smem8 = (F * NC + kHeadWarps * 4 * 8 + kHeadWarps * 8 * NC) * (int)sizeof(float);
+    if (smem8 <= 200 * 1024) {
+      static int attr8[64] = {};
+      int dev = 0;
+      MTB_CUDA_CHECK(cudaGetDevice(&dev));
+      if (dev < 0 || dev >= 64 || smem8 > attr8[dev]) {
+        MTB_CUDA_CHECK(cudaFuncSetAttribute(fc2_softmax_ce_rows8_kernel<10, T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            smem8));
+        if (dev >= 0 && dev < 64) attr8[dev] = smem8;
+      }
+      MTB_CUDA_CHECK(mtb::launch(fc2_softmax_ce_rows8_kernel<10, T>, dim3((B + 7) / 8), dim3(kHeadWarps * 32), (size_t)smem8,
+                                 stream, h, W, bias, labels, logits, probs, dlogits, loss_accum, err_accum, B, F, win_step,
+                                 win_rows));
+      return 0;
+    }
+  }
   const int smem = (F * NC + kHeadWarps * NC * 32) * (int)sizeof(float);
   MTB_REQUIRE(smem <= 200 * 1024, "fc2_softmax_ce_fast: weight matrix does not fit in shared memory");
   static int attr_bytes = 0;

@@ -136,8 +136,8 @@ def fused(comm, outdir):
 
 
 def train(comm, outdir):
-    cfg = TrainConfig(model="official1024", batch=100, max_steps=30, eval_every=0, log_every=10,
-                      dropout=True, step_timeout_s=60)
+    cfg = TrainConfig(model="official1024", batch=100, max_steps=30, eval_every=10, log_every=10, profile_phases=True,
+                      dropout=True, step_timeout_s=60, log_jsonl=os.path.join(outdir, f"log_rank{comm.rank}.jsonl"))
     tr = Trainer(cfg, comm)
     tr.load_data()
     res = tr.fit()
@@ -149,6 +149,13 @@ def train(comm, outdir):
     if comm.rank == 0:
         with open(os.path.join(outdir, "result.json"), "w") as f:
             json.dump({k: v for k, v in res.items() if k != "phases_ms"}, f)
+        # the log line carries what SURVEY section 5 asks for: train / test error, per-phase times, bus bandwidth
+        recs = [json.loads(l) for l in open(os.path.join(outdir, "log_rank0.jsonl"))]
+        line = [r for r in recs if r.get("step") == 20][0]
+        for k in ("loss", "lr", "train_error", "test_error", "img_per_s", "fwd_us", "bwd_us", "allreduce_us",
+                  "allreduce_exposed_us", "bus_gbs"):
+            assert k in line, (k, line)
+        assert 0.0 <= line["train_error"] <= 100.0 and line["allreduce_us"] > 0 and line["bus_gbs"] > 0, line
     tr.close()
     comm.barrier()
     # the fp32 / TF32 path over the same fused allreduce (full fp32 parameter broadcast, no bf16 shadow)
