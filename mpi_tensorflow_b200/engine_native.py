@@ -208,6 +208,7 @@ class NativeEngine:
         self._can_window = self.conv1_tc and self._fast_head
         self._windowed = False
         self._stream_buf = None
+        self._stream_u8 = False
         # conv2: implicit GEMM (no im2col) when the shape has a shift-GEMM kernel, else im2col + GEMM
         want = self.conv_impl
         have = bool(N.lib().mtb_conv2_supported(14, s.c1, s.c2)) and not self.fp32
@@ -846,6 +847,11 @@ class NativeEngine:
                 raise RuntimeError(f"step {step_no}: no error count arrived from the device within {timeout:.0f}s")
 
     def _step_body(self, peers: bool = True):
+        if self._stream_buf is not None and self._stream_u8:
+            # host-streamed raw pixels: (u8 - 127.5) / 255 as extract_data does on the host (mpipy.py:215), on the device
+            st = self._stream_state
+            N.call("mtb_normalize_u8_dev", st["u8"][self._stream_buf].data_ptr(), st["x"][self._stream_buf].data_ptr(),
+                   self.B * 784)
         if self.conv1_tc:
             self._forward(self.B, True, True, zero=True)
         else:
@@ -923,7 +929,8 @@ class NativeEngine:
             self.p2p.barrier()
             self._rs_dirty = False
         self._windowed = mode == "window"
-        self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
+        self._stream_buf = int(mode[-1]) if "stream" in mode else None
+        self._stream_u8 = mode.startswith("ustream")
         if self.cfg.cuda_graph:
             key = mode if peers or self.world == 1 else mode + "/local"
             if key not in self._graphs:
@@ -951,8 +958,9 @@ class NativeEngine:
         B, dev = self.B, self.device
         if not (hx.is_pinned() and hy.is_pinned()):
             raise ValueError("stream_steps needs pinned host tensors (tensor.pin_memory())")
-        if hy.dtype != torch.int32 or hx.dtype != torch.float32:
-            raise ValueError("stream_steps needs float32 images and int32 labels")
+        u8 = hx.dtype == torch.uint8                 # raw pixels as the IDX files hold them: a quarter of the bytes per copy
+        if hy.dtype != torch.int32 or hx.dtype not in (torch.float32, torch.uint8):
+            raise ValueError("stream_steps needs float32 (normalised) or uint8 (raw) images and int32 labels")
         hx = hx.view(hx.shape[0], -1)
         rows = hx.shape[0]
         if rows < B:
@@ -965,6 +973,9 @@ class NativeEngine:
                 consumed=[torch.cuda.Event() for _ in range(self._STREAM_BUFS)],
                 copy=torch.cuda.Stream(device=dev),
             )
+        if u8 and "u8" not in self._stream_state:
+            self._stream_state["u8"] = [torch.empty(B, 784, dtype=torch.uint8, device=dev)
+                                        for _ in range(self._STREAM_BUFS)]
         st = self._stream_state
         ring = max(1, min(ring, self._MAIL_RING - 1))
         main = torch.cuda.current_stream()
@@ -980,13 +991,15 @@ class NativeEngine:
             o = ((self.opt_step * B) % (rows - B)) if rows > B else 0
             copy.wait_event(st["consumed"][k])                 # the step that used this half has copied it out
             with torch.cuda.stream(copy):
-                st["x"][k].copy_(hx[o:o + B], non_blocking=True)
+                (st["u8"] if u8 else st["x"])[k].copy_(hx[o:o + B], non_blocking=True)
                 st["y"][k].copy_(hy[o:o + B], non_blocking=True)
                 st["ready"][k].record(copy)
             main.wait_event(st["ready"][k])
-            if direct:                                         # one graph per half: no device-to-device copy
-                self._run_step(f"stream{k}", peers)
+            if direct:                                         # one graph per slot: no device-to-device copy
+                self._run_step(f"ustream{k}" if u8 else f"stream{k}", peers)
             else:
+                if u8:
+                    N.call("mtb_normalize_u8_dev", st["u8"][k].data_ptr(), st["x"][k].data_ptr(), B * 784)
                 self.x_in[:B].copy_(st["x"][k], non_blocking=True)
                 self.y_in[:B].copy_(st["y"][k], non_blocking=True)
                 self._run_step("staged", peers)
@@ -1004,7 +1017,8 @@ class NativeEngine:
         resident shard's window inside the kernels; ``/local`` variants skip the cross-GPU reduction."""
         key = key or mode
         self._windowed = mode == "window"
-        self._stream_buf = int(mode[-1]) if mode.startswith("stream") else None
+        self._stream_buf = int(mode[-1]) if "stream" in mode else None
+        self._stream_u8 = mode.startswith("ustream")
         snap = [t.clone() for t in (self.flat_params, self.shadow, self.dev_step, *self.slots)]
         if self.p2p is not None:
             self.p2p.barrier()

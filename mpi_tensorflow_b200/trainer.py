@@ -164,12 +164,18 @@ class Trainer:
         """Train ``steps`` steps from a dataset kept in host memory, one host->device batch copy
         and one device->host loss read per step (the reference's feed loop, ``mpipy.py:79-85``),
         with copies overlapped with compute on the GPU engine.  ``images`` [rows,28,28,1] or
-        [rows,784] float32, ``labels`` [rows] integer; they are pinned here if they are not
-        already.  Returns the list of per-step losses."""
-        x = torch.as_tensor(images, dtype=torch.float32)
+        [rows,784], float32 (already normalised) or uint8 (raw pixels as the IDX files hold them:
+        a quarter of the bytes per copy, normalised by the first kernel of the step as
+        ``extract_data`` does on the host); ``labels`` [rows] integer.  They are pinned here if
+        they are not already.  Returns the list of per-step losses."""
+        x = torch.as_tensor(images)
+        if x.dtype != torch.uint8:                   # uint8 = raw pixels: normalised on the device by the GPU engine
+            x = x.to(torch.float32)
         y = torch.as_tensor(labels).to(torch.int32)
         if not self._fused or not hasattr(self.engine, "stream_steps") or self.cfg.sync == "weight_avg":
             B, rows = self.cfg.batch, x.shape[0]
+            if x.dtype == torch.uint8:
+                x = (x.to(torch.float32) - 127.5) / 255.0                       # extract_data, mpipy.py:215
             out = []
             for i in range(steps):
                 o = (self.global_step * B) % (rows - B) if rows > B else 0       # mpipy.py:80-82, global step

@@ -125,6 +125,25 @@ def test_fit_stream_matches_stepwise_training():
     assert la[-1] < la[0] and lb[-1] < lb[0]
 
 
+def test_fit_stream_from_raw_uint8_pixels():
+    """fit_stream on the dataset's raw uint8 pixels (a quarter of the bytes over PCIe, normalised by the first kernel of
+    the step) trains exactly like fit_stream on the host-normalised float32 images."""
+    dev = torch.device("cuda", 0)
+    u8, lab = D.synthetic_mnist(512, 3)
+    x32 = torch.from_numpy(D.normalize_u8(u8).reshape(512, 28, 28, 1))
+    xu8 = torch.from_numpy(u8.reshape(512, 28, 28, 1))
+    y = torch.from_numpy(lab.astype(np.int32))
+    cfg = _cfg(batch=64, lr=0.02, dropout=True, lr_decay_rows=10 ** 9)
+    a = Trainer(cfg, device=dev)
+    la = a.fit_stream(x32, y, 12)
+    b = Trainer(cfg, device=dev)
+    lb = b.fit_stream(xu8, y, 12)
+    assert np.allclose(la[:3], lb[:3], rtol=5e-3, atol=5e-3), (la[:3], lb[:3])
+    assert lb[-1] < lb[0]
+    a.close()
+    b.close()
+
+
 def test_loss_mailbox_matches_device_accumulator():
     """The loss the update kernel mails into pinned host memory is the device accumulator's
     value for exactly that step (step number and value travel in one 8-byte store)."""
