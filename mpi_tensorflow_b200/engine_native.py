@@ -69,8 +69,9 @@ class NativeEngine:
                          and cfg.comm_algo not in ("oneshot", "push") and not self._lp)
         # bucketed overlap (default): the fc bucket's fused allreduce+update runs on the comm stream under the
         # convolution backward; the reduce-scatter GEMM needs the single whole-buffer launch instead
-        # (a lone GPU has no flag round or NVLink latency to hide, but the 72 MB of the update itself still hide
-        # under the convolutions: 213.6 vs 219.3 us per step; MTB_OVERLAP_N1=0 gives the single launch back)
+        # (a lone GPU has no flag round or NVLink latency to hide, but the 72 MB of the update itself still hide under
+        # the convolutions: 213.6 vs 219.3 us per step at batch 1024, 111.3 vs 113.4 at batch 100; MTB_OVERLAP_N1=0
+        # gives the single launch back)
         self._overlap = (bool(cfg.overlap) and not self._rs_mode
                          and (self.world > 1 or os.environ.get("MTB_OVERLAP_N1", "1") != "0"))
         self._rs_active = False                  # True only inside the fused step body
