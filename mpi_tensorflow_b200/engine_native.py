@@ -271,38 +271,49 @@ class NativeEngine:
             torch.cuda.synchronize()
 
     # -- state that the two-shot / nvls update keeps only with the owner of each slice ------------
+    @staticmethod
+    def owned_slice(lo: int, hi: int, rank: int, world: int):
+        """Rank ``rank``'s slice of an owner-sliced K1 launch over elements [lo, hi): the kernel's own arithmetic
+        (``allreduce_fused.cu``: ``per = ceil(vectors / world)`` vectors of 4 elements per rank)."""
+        vecs = (hi - lo) // 4
+        per = (vecs + world - 1) // world
+        olo = lo + min(per * rank, vecs) * 4
+        return olo, min(olo + per * 4, hi)
+
+    @staticmethod
+    def contribution_pieces(rank: int, world: int, sliced, lo: int, hi: int):
+        """Which parts of [lo, hi) rank ``rank`` contributes when a buffer is completed across ranks: inside each
+        owner-sliced bucket of ``sliced`` (a collection of (blo, bhi)) its own slice; everything outside those buckets
+        (updated in full by every rank) comes from rank 0.  Over all ranks the pieces tile [lo, hi) exactly once."""
+        out = []
+        buckets = sorted(sliced)
+        for blo, bhi in buckets:
+            olo, ohi = NativeEngine.owned_slice(blo, bhi, rank, world)
+            a, b = max(lo, olo), min(hi, ohi)
+            if b > a:
+                out.append((a, b))
+        if rank == 0:
+            cur = lo
+            for blo, bhi in buckets + [(hi, hi)]:
+                a, b = max(cur, lo), min(blo, hi)
+                if b > a:
+                    out.append((a, b))
+                cur = max(cur, bhi)
+        return sorted(out)
+
     def _owned_ranges(self):
         """Element ranges of the flat buffers whose optimizer state (and sharded fp32 master) only THIS rank
-        maintains: its slice of every owner-sliced K1 launch made so far.  The kernel slices each launch's own
-        [lo, hi) (``allreduce_fused.cu``: ``per = ceil(vectors / world)``), so with bucketed launches ownership is
-        per bucket, not a slice of the whole buffer."""
-        out = []
-        for (lo, hi) in sorted(self._sliced):
-            vecs = (hi - lo) // 4
-            per = (vecs + self.world - 1) // self.world
-            olo = lo + min(per * self.p2p.rank, vecs) * 4
-            out.append((olo, min(olo + per * 4, hi)))
-        return out
+        maintains: its slice of every owner-sliced K1 launch made so far.  With bucketed launches ownership is per
+        bucket, not a slice of the whole buffer."""
+        return [self.owned_slice(lo, hi, self.p2p.rank, self.world) for (lo, hi) in sorted(self._sliced)]
 
     def _gather_owned(self, buf: torch.Tensor, ranges):
-        """Make ``buf`` complete on every rank.  Inside owner-sliced buckets each rank contributes the part it owns;
-        everything else (buckets every rank updates in full) comes from rank 0.  Parts are summed, so every element
-        has exactly one contributor.  Collective; used at checkpoint / inspection time."""
-        owned = self._owned_ranges()
-        sliced = sorted(self._sliced)
+        """Make ``buf`` complete on every rank: every element has exactly one contributing rank
+        (:meth:`contribution_pieces`) and the parts are summed.  Collective; used at checkpoint / inspection time."""
         for lo, hi in ranges:
             seg = torch.zeros(hi - lo, device=self.device)
-            for olo, ohi in owned:
-                a, b = max(lo, olo), min(hi, ohi)
-                if b > a:
-                    seg[a - lo:b - lo] = buf[a:b]
-            if self.p2p.rank == 0:                        # the complement of the sliced buckets
-                cur = lo
-                for blo, bhi in sliced + [(hi, hi)]:
-                    a, b = max(cur, lo), min(blo, hi)
-                    if b > a:
-                        seg[a - lo:b - lo] = buf[a:b]
-                    cur = max(cur, bhi)
+            for a, b in self.contribution_pieces(self.p2p.rank, self.world, list(self._sliced), lo, hi):
+                seg[a - lo:b - lo] = buf[a:b]
             self.p2p.allreduce(seg, average=False)
             buf[lo:hi] = seg
 

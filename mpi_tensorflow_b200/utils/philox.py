@@ -54,14 +54,22 @@ def philox4x32(c0, c1, c2, c3, k0, k1, rounds: int = 10):
 
 
 def random_u32(n: int, seed: int, stream: int, purpose: int, offset: int = 0) -> np.ndarray:
-    """``n`` uint32 values for element indices ``offset .. offset+n``."""
-    idx = np.arange(offset, offset + n, dtype=np.uint64)
-    blk = (idx // np.uint64(4)).astype(np.uint32)
-    lane = (idx % np.uint64(4)).astype(np.int64)
-    w = philox4x32(blk, np.uint32(stream & 0xFFFFFFFF), np.uint32((stream >> 32) & 0xFFFFFFFF),
-                   np.uint32(purpose), seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    stacked = np.stack(w, axis=0)                     # [4, n]
-    return stacked[lane, np.arange(n)]
+    """``n`` uint32 values for element indices ``offset .. offset+n``.  One Philox evaluation yields the four
+    words of a block of four consecutive indices, so only the blocks that are touched are evaluated (in chunks,
+    to bound the temporaries)."""
+    if n <= 0:
+        return np.empty(0, dtype=np.uint32)
+    b0, b1 = offset // 4, (offset + n + 3) // 4
+    out = np.empty((b1 - b0) * 4, dtype=np.uint32)
+    chunk = 1 << 20
+    for lo in range(b0, b1, chunk):
+        hi = min(b1, lo + chunk)
+        blk = np.arange(lo, hi, dtype=np.uint64).astype(np.uint32)
+        w = philox4x32(blk, np.uint32(stream & 0xFFFFFFFF), np.uint32((stream >> 32) & 0xFFFFFFFF),
+                       np.uint32(purpose), seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+        out[(lo - b0) * 4:(hi - b0) * 4] = np.stack(w, axis=1).reshape(-1)
+    skip = offset - b0 * 4
+    return out[skip:skip + n]
 
 
 def uniform01(n: int, seed: int, stream: int, purpose: int, offset: int = 0) -> np.ndarray:

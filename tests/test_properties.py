@@ -149,3 +149,34 @@ def test_loss_mailbox_word_roundtrip(step, loss):
     if step + ring < 2 ** 32:
         with pytest.raises(RuntimeError):
             NativeEngine._await_loss(eng, step + ring)          # same slot, later step: not there yet
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Ownership of optimizer state under bucketed, owner-sliced K1 launches: when a buffer is completed
+# across ranks, every element must come from exactly one rank, and inside a sliced bucket from the rank whose
+# slice the kernel's arithmetic (per = ceil(vectors / world)) says it is.
+@settings(max_examples=60, deadline=None)
+@given(world=st.integers(1, 8), n4=st.integers(8, 400), cuts=st.lists(st.integers(0, 400), min_size=0, max_size=4),
+       lo4=st.integers(0, 200), span4=st.integers(1, 300))
+def test_sliced_bucket_ownership_tiles_every_range(world, n4, cuts, lo4, span4):
+    from mpi_tensorflow_b200.engine_native import NativeEngine as E
+    n = 4 * n4
+    pts = sorted({min(4 * c, n) for c in cuts} | {0, n})
+    buckets = [(a, b) for a, b in zip(pts[:-1], pts[1:])][::2]          # every other interval is an owner-sliced bucket
+    lo = min(4 * lo4, n - 4)
+    hi = min(n, lo + 4 * span4)
+    cover = np.zeros(n, dtype=np.int32)
+    for r in range(world):
+        for a, b in E.contribution_pieces(r, world, buckets, lo, hi):
+            assert lo <= a < b <= hi
+            cover[a:b] += 1
+    assert (cover[lo:hi] == 1).all() and cover[:lo].sum() == 0 and cover[hi:].sum() == 0
+    for blo, bhi in buckets:                                            # slices of one bucket partition it, in rank order
+        prev = blo
+        for r in range(world):
+            olo, ohi = E.owned_slice(blo, bhi, r, world)
+            assert olo == prev or olo == ohi or (olo >= prev and ohi <= bhi)
+            if ohi > olo:
+                assert olo == prev
+                prev = ohi
+        assert prev == bhi
