@@ -48,9 +48,11 @@ def test_one_step_grads_match_bf16_oracle(model, batch, dropout):
         g = grads[p.offset:p.offset + p.numel]
         r = rg[p.key].reshape(-1)
         rel = float((g - r).norm() / (r.norm() + 1e-12))
-        # conv1 runs on fp32 inputs/weights on the device while the oracle rounds them to bf16,
-        # and its gradient sits at the end of the longest bf16 chain
-        tol = 6e-2 if p.layer == "conv1" else 3e-2
+        # Bounds set from measurements over several seeds (profiles/r2/engine_vs_oracle_errors.txt: conv1 <= 2.3e-2,
+        # conv2 <= 1.4e-2, fc1 <= 8.9e-3, fc2 <= 1.6e-3), about 1.5x the worst seen.  The error grows towards the input
+        # because every layer boundary rounds to bf16 once more, and conv1 runs on fp32 inputs / weights on the device
+        # while the oracle rounds them to bf16.  A 2 % systematic error in any layer from conv2 up now fails.
+        tol = {"conv1": 3.5e-2, "conv2": 2.2e-2, "fc1": 1.4e-2, "fc2": 4e-3}[p.layer]
         assert rel < tol, f"{p.key}: rel err {rel}"
 
 
