@@ -21,7 +21,6 @@ actual loop), device-timed, max over ranks.
 from __future__ import annotations
 
 import os
-import time
 
 import numpy as np
 import torch

@@ -17,9 +17,14 @@ reported as the max over ranks:
           126 MB L2, streamed sequentially so every step's batch is cold) lives in HBM and
           the whole step (window copy, forward, backward, fused allreduce+update) is one
           CUDA-graph launch with no host sync.
-  e2e     the same step through the public ``Trainer.step(images, labels)`` call with every
-          batch copied from pinned host memory inside the timed region and the loss read
-          back to the host every step.
+  e2e     the same step through the public ``Trainer.fit_stream(host_images, host_labels, steps)``
+          call: every step's batch (raw uint8 pixels + int32 labels) is copied from pinned host
+          memory inside the timed region and every step's loss and error count are read on the
+          host (the synchronous one-call-per-step form ``Trainer.step(images, labels)`` is timed
+          too and reported beside it).
+
+``--reference-semantics`` times the reference's own schedule instead (local steps, root-only
+weight average every 50 steps, full test-shard eval every step): BASELINE.md section 3, B-faithful.
 
 ``--impl reference`` would run the unmodified reference from baseline/_ref; it cannot be
 installed on this image (no setup.py, needs TensorFlow 1.x + mpi4py + Python 2 + a missing
@@ -34,7 +39,6 @@ import os
 import statistics
 import sys
 import threading
-import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -214,7 +218,7 @@ def run_ours(args) -> dict:
     e2e = None
     if not args.no_e2e:
         # the public training call on a HOST dataset: Trainer.fit_stream copies every step's batch
-        # from pinned host memory (copy stream, double buffered) and reads every step's loss back
+        # from pinned host memory (copy stream, 4-slot input ring) and reads every step's loss back
         hrows = min(rows, 32 * B)
         # ... as RAW uint8 pixels, the form the dataset has on disk (mpipy.py:215 normalises on the host; the engine's
         # first kernel of the step does it on the device): 784 instead of 3136 bytes per image over PCIe.  With fp32

@@ -398,7 +398,7 @@ class NativeEngine:
         staged batch with a null step pointer."""
         if self._windowed:
             return self.data_x.data_ptr(), self.data_y.data_ptr(), self.dev_step.data_ptr(), self.rows
-        if self._stream_buf is not None:         # host-streamed training: read the half of the double buffer directly
+        if self._stream_buf is not None:         # host-streamed training: read the slot of the input ring directly
             st = self._stream_state
             return st["x"][self._stream_buf].data_ptr(), st["y"][self._stream_buf].data_ptr(), None, 0
         return self.x_in.data_ptr(), self.y_in.data_ptr(), None, 0

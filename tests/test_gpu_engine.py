@@ -107,7 +107,7 @@ def test_wide_preset_runs():
 
 
 def test_fit_stream_matches_stepwise_training():
-    """Host-streamed training (double-buffered H2D, lagged loss reads) gives the same losses as
+    """Host-streamed training (H2D prefetch into a ring of input buffers, lagged loss reads) gives the same losses as
     calling step(images, labels) synchronously on the same windows."""
     dev = torch.device("cuda", 0)
     sh = _shards(512)
@@ -181,7 +181,7 @@ def test_loss_mailbox_matches_device_accumulator():
 def test_fused_step_loss_equals_unfused_loss(monkeypatch):
     """Same API, one meaning: the loss of the fused graph step (mailed by K1) is the loss compute_grads returns for
     the same batch and weights, CE + 5e-4 * L2 as in the reference (mpipy.py:55-58)."""
-    monkeypatch.setenv("MTB_OVERLAP_N1", "1")        # bucketed K1 on a lone GPU too (default there: one launch)
+    monkeypatch.setenv("MTB_OVERLAP_N1", "1")        # bucketed K1 on a lone GPU (the default; the variable can turn it off)
     dev = torch.device("cuda", 0)
     sh = _shards(256)
     x = torch.from_numpy(sh.train_x[:64])

@@ -294,3 +294,23 @@ def test_crash_then_resume_matches_uninterrupted_run(tmp_path):
     assert set(want) == set(got) and len(want) >= 9
     for k in want:
         assert np.array_equal(want[k], got[k]), k
+
+
+def test_fit_stream_accepts_raw_uint8_pixels():
+    """``fit_stream`` takes the dataset as raw uint8 pixels (what the IDX files hold) as well as host-normalised
+    float32: both train identically (the CPU engine normalises on the host, ``(x - 127.5) / 255`` as ``extract_data``
+    does for the reference, ``mpipy.py:215``; the GPU engine does it in the first kernel of the step)."""
+    u8, lab = D.synthetic_mnist(96, 5)
+    x32 = D.normalize_u8(u8).reshape(96, 28, 28, 1)
+    cfg = TrainConfig(model="tiny", batch=16, device="cpu", eval_every=0, log_every=0, dropout=False)
+    a = Trainer(cfg)
+    la = a.fit_stream(x32, lab, 7)
+    b = Trainer(cfg)
+    lb = b.fit_stream(u8.reshape(96, 28, 28, 1), lab, 7)
+    assert a.global_step == b.global_step == 7
+    assert np.allclose(la, lb, rtol=0, atol=0)
+    # the window walks on from the global step (the reference's offset arithmetic), also across calls
+    lc = a.fit_stream(x32, lab, 3) + []
+    d = Trainer(cfg)
+    ld = d.fit_stream(x32, lab, 10)
+    assert np.allclose(la + lc, ld, rtol=0, atol=0)
