@@ -209,7 +209,7 @@ def run_ours(args) -> dict:
     per_step_kernels = getattr(eng, "launches_per_step", None)
     host_calls = N.LAUNCHES - launches0
     launches = (per_step_kernels * K + host_calls) if (per_step_kernels and cfg.cuda_graph) else host_calls
-    last = float(eng.loss_acc.item())
+    last = float(eng._await_loss(eng.opt_step))          # the same quantity as `first`: CE + L2 of the last step, mailed by K1
     if hasattr(comm, "check_status"):
         comm.check_status()
     value = n * B * K / (ms / 1e3)
