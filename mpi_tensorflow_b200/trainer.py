@@ -135,9 +135,14 @@ class Trainer:
         if images is None:
             if self.sampler is None:
                 raise RuntimeError("no data: call load_data() or pass a batch")
-            if hasattr(self.engine, "resident_batch"):
+            if hasattr(self.engine, "resident_batch") and isinstance(self.sampler, D.SequentialSampler):
+                # the GPU engine walks the reference's sequential window over its resident shard on the device
                 images, labels = self.engine.resident_batch(self.sampler, step)
             else:
+                # any other sampler (sampler="shuffle") picks its rows on the host and feeds them like a caller's batch
+                if self.shards is None:
+                    raise RuntimeError(f"sampler={self.cfg.sampler!r} needs the host shards (load_data()); a dataset "
+                                       f"attached on the device is walked with the sequential window only")
                 idx = self.sampler.indices(step)
                 images, labels = self.shards.train_x[idx], self.shards.train_y[idx]
         if self._fused:

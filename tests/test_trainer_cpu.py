@@ -314,3 +314,44 @@ def test_fit_stream_accepts_raw_uint8_pixels():
     d = Trainer(cfg)
     ld = d.fit_stream(x32, lab, 10)
     assert np.allclose(la + lc, ld, rtol=0, atol=0)
+
+
+def test_shuffle_sampler_is_honoured_by_an_engine_with_a_resident_shard():
+    """An engine that keeps the shard on the device walks it with the sequential window itself; any other sampler
+    must not be silently replaced by that window: its rows are picked on the host and fed as a batch."""
+    import types
+    seen = []
+
+    class StubEngine:
+        can_fuse, name, flat_params, slots = True, "stub", torch.zeros(4), []
+
+        def attach_dataset(self, shards):
+            pass
+
+        def resident_batch(self, sampler, step):
+            return None, None
+
+        def fused_step(self, images, labels, lr, step, read_loss=True, peers=True):
+            seen.append(None if images is None else np.asarray(labels).copy())
+            return 0.0
+
+    u8, lab = D.synthetic_mnist(64, 2)
+    x = D.normalize_u8(u8).reshape(64, 28, 28, 1)
+    sh = D.Shards(x, lab.astype(np.int64), x[:16], lab[:16].astype(np.int64), x[:16], lab[:16].astype(np.int64))
+    for sampler in ("sequential", "shuffle"):
+        seen.clear()
+        tr = Trainer(TrainConfig(model="tiny", batch=16, device="cpu", sampler=sampler, eval_every=0, log_every=0),
+                     engine=StubEngine())
+        tr.load_data(sh)
+        for _ in range(3):
+            tr.step()
+        if sampler == "sequential":
+            assert all(s is None for s in seen)                     # the engine gathers the window itself
+        else:
+            want = [sh.train_y[tr.sampler.indices(i)] for i in range(3)]
+            assert all(np.array_equal(a, b) for a, b in zip(seen, want))
+    tr2 = Trainer(TrainConfig(model="tiny", batch=16, device="cpu", sampler="shuffle", eval_every=0, log_every=0),
+                  engine=StubEngine())
+    tr2.sampler = D.ShuffleSampler(64, 16)
+    with pytest.raises(RuntimeError):
+        tr2.step()
