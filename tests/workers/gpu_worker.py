@@ -56,6 +56,19 @@ def algebra(comm):
         assert np.array_equal(b.cpu().numpy(), full[n - 1]), ("bcast", count)
     for _ in range(50):
         comm.barrier()
+    # Flag-protocol stress ("race detection": compute-sanitizer is closed on this pool): 1000 device
+    # barriers queued back to back with no host synchronisation between them (sequence numbers only ever grow, a rank
+    # may run several rounds ahead of a slow peer), then 100 allreduces of varying small sizes whose exact result shows
+    # at once if any rank ever read a peer's buffer from the wrong round.
+    for _ in range(1000):
+        comm.device_barrier()
+    torch.cuda.synchronize()
+    comm.check_status()
+    sizes = np.random.default_rng(7).integers(1, 5000, size=100)       # the same sequence on every rank
+    for it, count in enumerate(sizes):
+        t = torch.full((int(count),), float(r + 1 + it), device=dev)
+        comm.allreduce(t, average=False)
+        assert bool((t == float(n * (n + 1) // 2 + n * it)).all()), ("stress allreduce", it, int(count))
     print(f"GPU_COMM_OK rank {r}/{n}", flush=True)
 
 
